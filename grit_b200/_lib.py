@@ -1,0 +1,110 @@
+"""ctypes binding of grit_b200/csrc/libgritpack.so (the C ABI in include/gritpack.h).
+
+There is no fallback: if the shared library is missing or the device is not a
+B200-class GPU, the calls raise.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "libgritpack.so")
+
+PAGE = 4096
+MAX_PAGES = 1 << 26
+KIND_ZERO, KIND_DATA, KIND_DUP, KIND_PARENT, KIND_PEER = range(5)
+OK, EINVAL, ECUDA, EIO, ECRC, EFORMAT, ENOMEM = 0, -1, -2, -3, -4, -5, -6
+
+
+class GritError(RuntimeError):
+    def __init__(self, code, message):
+        super().__init__(f"gritpack error {code}: {message}")
+        self.code = code
+        self.message = message
+
+
+class Table(C.Structure):
+    _fields_ = [("hash", C.c_void_p), ("crc", C.c_void_p), ("n_pages", C.c_uint64)]
+
+
+class PackStats(C.Structure):
+    _fields_ = [(n, C.c_uint64) for n in ("n_pages", "n_zero", "n_data", "n_dup", "n_parent", "n_peer")] + [
+        ("gpu_ms", C.c_double)]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+class RestoreStats(C.Structure):
+    _fields_ = [("n_pages", C.c_uint64), ("n_bad", C.c_uint64), ("first_bad", C.c_uint64), ("gpu_ms", C.c_double)]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+class Opts(C.Structure):
+    _fields_ = [("struct_size", C.c_uint32), ("device", C.c_int32), ("verify", C.c_uint32),
+                ("io_threads", C.c_uint32), ("chunk_bytes", C.c_uint64), ("parent_dir", C.c_char_p)]
+
+
+class Stats(C.Structure):
+    _fields_ = [(n, C.c_uint64) for n in ("bytes_logical", "bytes_stored", "n_files", "n_dirs", "n_pages", "n_zero",
+                                          "n_data", "n_dup", "n_parent", "n_peer", "n_bad")] + [
+        (n, C.c_double) for n in ("seconds", "gpu_ms", "h2d_bytes", "d2h_bytes")]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+# every symbol include/gritpack.h declares: name -> (restype, argtypes)
+_ERR = [C.c_char_p, C.c_size_t]
+_P, _U64, _U32, _I = C.c_void_p, C.c_uint64, C.c_uint32, C.c_int
+SYMBOLS = {
+    "grit_version": (_I, []),
+    "grit_crc32c": (_U32, [_U32, _P, C.c_size_t]),
+    "grit_ctx_create": (_I, [_I, C.POINTER(_P)] + _ERR),
+    "grit_ctx_destroy": (None, [_P]),
+    "grit_ctx_launches": (_U64, [_P]),
+    "grit_analyze_pages": (_I, [_P, _P, _U64, _P, _P, _P, _P] + _ERR),
+    "grit_dedup_pages": (_I, [_P, _U64, _P, _P, _P, C.POINTER(Table), C.POINTER(Table), _U32, _P] + _ERR),
+    "grit_compact_pages": (_I, [_P, _P, _U64, _P, _P, _U64, _U64, C.POINTER(_U64), _P] + _ERR),
+    "grit_pack_buffer": (_I, [_P, _P, _U64, C.POINTER(Table), C.POINTER(Table), _U32, _P, _U64, _P, _P, _P,
+                              C.POINTER(PackStats), _P] + _ERR),
+    "grit_restore_buffer": (_I, [_P, _P, _U64, _P, _P, _U64, _P, _U64, C.POINTER(_P), C.POINTER(_U64), _U32, _P, _I,
+                                 C.POINTER(RestoreStats), _P] + _ERR),
+    "grit_synth_image": (_I, [_P, _P, _U64, _U64, _U64, _U32, _U32, _U32, _P] + _ERR),
+    "grit_pack_host": (_I, [_P, _P, _U64, C.POINTER(Table), _P, _U64, _P, _P, _P, C.POINTER(PackStats)] + _ERR),
+    "grit_restore_host": (_I, [_P, _P, _U64, _P, _P, _U64, _P, _U64, _P, _I, C.POINTER(RestoreStats)] + _ERR),
+    "grit_pin_host": (_I, [_P, C.c_size_t]),
+    "grit_unpin_host": (_I, [_P]),
+    "grit_pack_dir": (_I, [C.c_char_p, C.c_char_p, C.POINTER(Opts), C.POINTER(Stats)] + _ERR),
+    "grit_restore_dir": (_I, [C.c_char_p, C.c_char_p, C.POINTER(Opts), C.POINTER(Stats)] + _ERR),
+    "grit_write_sentinel": (_I, [C.c_char_p, C.c_char_p]),
+}
+
+_lib = None
+
+
+def load():
+    """Loads libgritpack.so and types every entry point; raises if it is not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise GritError(ECUDA, f"{LIB_PATH} is not built; run `make -C grit_b200/csrc` "
+                               "(or __graft_entry__.build()); there is no fallback path")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SYMBOLS.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(rc, err):
+    if rc != 0:
+        raise GritError(rc, err.value.decode(errors="replace"))
+
+
+def errbuf():
+    return C.create_string_buffer(1024)

@@ -1,0 +1,322 @@
+// C ABI over the page kernels: context, stage entry points, pack/restore of a
+// device-resident image.  Declarations and reference citations: include/gritpack.h.
+#include <new>
+
+#include "ctx.h"
+
+using namespace grit;
+
+namespace grit {
+
+int ensure_table(grit_ctx* ctx, uint64_t n_items, DedupTable* t, char* err, size_t errlen) {
+  uint64_t cap = 1024;
+  while (cap < 2 * n_items) cap <<= 1;
+  if (cap > ctx->table_cap) {
+    if (ctx->d_keys) cudaFree(ctx->d_keys);
+    if (ctx->d_vals) cudaFree(ctx->d_vals);
+    ctx->d_keys = nullptr;
+    ctx->d_vals = nullptr;
+    ctx->table_cap = 0;
+    GRIT_CUDA(cudaMalloc(&ctx->d_keys, cap * sizeof(unsigned long long)));
+    GRIT_CUDA(cudaMalloc(&ctx->d_vals, cap * sizeof(uint32_t)));
+    ctx->table_cap = cap;
+  }
+  t->keys = ctx->d_keys;
+  t->vals = ctx->d_vals;
+  t->mask = cap - 1;
+  return GRIT_OK;
+}
+
+int ensure_status(grit_ctx* ctx, uint64_t n_pages, char* err, size_t errlen) {
+  const uint64_t tiles = (n_pages + kCompactTile - 1) / kCompactTile + 1;
+  if (tiles > ctx->status_cap) {
+    if (ctx->d_status) cudaFree(ctx->d_status);
+    ctx->d_status = nullptr;
+    ctx->status_cap = 0;
+    GRIT_CUDA(cudaMalloc(&ctx->d_status, tiles * sizeof(unsigned long long)));
+    ctx->status_cap = tiles;
+  }
+  return GRIT_OK;
+}
+
+int reset_counters(grit_ctx* ctx, cudaStream_t s, char* err, size_t errlen) {
+  GRIT_CUDA(cudaMemsetAsync(ctx->d_cnt, 0, sizeof(DevCounters), s));
+  GRIT_CUDA(cudaMemsetAsync(&ctx->d_cnt->first_bad, 0xFF, sizeof(unsigned long long), s));
+  return GRIT_OK;
+}
+
+int read_counters(grit_ctx* ctx, cudaStream_t s, char* err, size_t errlen) {
+  GRIT_CUDA(cudaMemcpyAsync(ctx->h_cnt, ctx->d_cnt, sizeof(DevCounters), cudaMemcpyDeviceToHost, s));
+  GRIT_CUDA(cudaStreamSynchronize(s));
+  return GRIT_OK;
+}
+
+}  // namespace grit
+
+namespace {
+
+cudaStream_t pick(grit_ctx* ctx, void* stream) { return stream ? static_cast<cudaStream_t>(stream) : ctx->stream; }
+
+int enter(grit_ctx* ctx, char* err, size_t errlen) {
+  if (!ctx) return fail(err, errlen, GRIT_EINVAL, "null context");
+  GRIT_CUDA(cudaSetDevice(ctx->device));
+  return GRIT_OK;
+}
+
+int check_pages(uint64_t n_pages, const void* p, char* err, size_t errlen) {
+  if (n_pages > GRIT_MAX_PAGES) return fail(err, errlen, GRIT_EINVAL, "n_pages %llu exceeds GRIT_MAX_PAGES", (unsigned long long)n_pages);
+  if (reinterpret_cast<uintptr_t>(p) & 15) return fail(err, errlen, GRIT_EINVAL, "buffer is not 16-byte aligned");
+  return GRIT_OK;
+}
+
+// table build + resolve, asynchronous on s
+int dedup_async(grit_ctx* ctx, uint64_t n_pages, const uint32_t* d_crc, const uint64_t* d_hash, uint32_t* d_ref,
+                const grit_table* parent, const grit_table* peers, uint32_t n_peers, cudaStream_t s, char* err,
+                size_t errlen) {
+  if (n_peers > GRIT_MAX_PEERS) return fail(err, errlen, GRIT_EINVAL, "n_peers %u > %u", n_peers, GRIT_MAX_PEERS);
+  uint64_t items = n_pages;
+  PeerCrcs crcs{};
+  if (parent && parent->n_pages) {
+    if (parent->n_pages > GRIT_MAX_PAGES) return fail(err, errlen, GRIT_EINVAL, "parent too large");
+    items += parent->n_pages;
+    crcs.parent = parent->crc;
+  }
+  for (uint32_t r = 0; r < n_peers; r++) {
+    if (peers[r].n_pages > GRIT_MAX_PAGES) return fail(err, errlen, GRIT_EINVAL, "peer too large");
+    items += peers[r].n_pages;
+    crcs.peer[r] = peers[r].crc;
+  }
+  DedupTable t{};
+  if (int rc = ensure_table(ctx, items, &t, err, errlen)) return rc;
+  GRIT_CUDA(cudaMemsetAsync(t.keys, 0, (t.mask + 1) * sizeof(unsigned long long), s));
+  GRIT_CUDA(cudaMemsetAsync(t.vals, 0xFF, (t.mask + 1) * sizeof(uint32_t), s));
+  if (parent && parent->n_pages) {
+    GRIT_CUDA(launch_table_insert(ctx->geom, t, parent->hash, nullptr, parent->n_pages, 0, 0, s));
+    ctx->launches++;
+  }
+  for (uint32_t r = 0; r < n_peers; r++)
+    if (peers[r].n_pages) {
+      GRIT_CUDA(launch_table_insert(ctx->geom, t, peers[r].hash, nullptr, peers[r].n_pages, 1 + r, 0, s));
+      ctx->launches++;
+    }
+  GRIT_CUDA(launch_table_insert(ctx->geom, t, d_hash, d_ref, n_pages, kOriginSelf, 0, s));
+  GRIT_CUDA(launch_resolve(ctx->geom, t, 0, n_pages, d_crc, d_hash, d_ref, crcs, s));
+  ctx->launches += 2;
+  return GRIT_OK;
+}
+
+int compact_async(grit_ctx* ctx, const void* d_image, uint64_t n_pages, uint32_t* d_ref, void* d_packed,
+                  uint64_t capacity_pages, uint64_t slot_base, cudaStream_t s, char* err, size_t errlen) {
+  if (int rc = ensure_status(ctx, n_pages, err, errlen)) return rc;
+  const uint64_t tiles = (n_pages + kCompactTile - 1) / kCompactTile;
+  GRIT_CUDA(cudaMemsetAsync(ctx->d_status, 0, tiles * sizeof(unsigned long long), s));
+  GRIT_CUDA(launch_compact(ctx->geom, d_image, n_pages, d_ref, d_packed, capacity_pages, slot_base, false, ctx->d_status,
+                           ctx->d_cnt, s));
+  ctx->launches++;
+  return GRIT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int grit_version(void) { return GRIT_ABI_VERSION; }
+
+int grit_ctx_create(int device, grit_ctx** out, char* err, size_t errlen) {
+  if (!out) return fail(err, errlen, GRIT_EINVAL, "out is null");
+  *out = nullptr;
+  int n_dev = 0;
+  cudaError_t e = cudaGetDeviceCount(&n_dev);
+  if (e != cudaSuccess || n_dev == 0)
+    return fail(err, errlen, GRIT_ECUDA, "no CUDA device (%s); gritpack has no CPU path",
+                e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+  if (device < 0 || device >= n_dev) return fail(err, errlen, GRIT_EINVAL, "device %d out of range (0..%d)", device, n_dev - 1);
+  GRIT_CUDA(cudaSetDevice(device));
+  cudaDeviceProp prop{};
+  GRIT_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10)
+    return fail(err, errlen, GRIT_ECUDA, "device %d is sm_%d%d; libgritpack is built for sm_100a only", device, prop.major,
+                prop.minor);
+  grit_ctx* ctx = new (std::nothrow) grit_ctx();
+  if (!ctx) return fail(err, errlen, GRIT_ENOMEM, "out of host memory");
+  ctx->device = device;
+  ctx->geom.sm_count = prop.multiProcessorCount;
+  auto bail = [&](int rc) {
+    grit_ctx_destroy(ctx);
+    return rc;
+  };
+#define CTX_CUDA(call)                                                                                  \
+  do {                                                                                                  \
+    cudaError_t e_ = (call);                                                                            \
+    if (e_ != cudaSuccess) return bail(fail(err, errlen, GRIT_ECUDA, "%s: %s", #call, cudaGetErrorString(e_))); \
+  } while (0)
+  CTX_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+  CTX_CUDA(cudaStreamCreateWithFlags(&ctx->h2d, cudaStreamNonBlocking));
+  CTX_CUDA(cudaStreamCreateWithFlags(&ctx->d2h, cudaStreamNonBlocking));
+  CTX_CUDA(cudaEventCreate(&ctx->ev0));
+  CTX_CUDA(cudaEventCreate(&ctx->ev1));
+  CTX_CUDA(cudaMalloc(&ctx->d_tables, sizeof(Gf2Tables)));
+  CTX_CUDA(cudaMalloc(&ctx->d_cnt, sizeof(DevCounters)));
+  CTX_CUDA(cudaMallocHost(&ctx->h_cnt, sizeof(DevCounters)));
+  {
+    Gf2Tables* h = new (std::nothrow) Gf2Tables();
+    if (!h) return bail(fail(err, errlen, GRIT_ENOMEM, "out of host memory"));
+    build_gf2_tables(h);
+    cudaError_t ce = cudaMemcpy(ctx->d_tables, h, sizeof(Gf2Tables), cudaMemcpyHostToDevice);
+    delete h;
+    CTX_CUDA(ce);
+  }
+  CTX_CUDA(configure_kernels());
+#undef CTX_CUDA
+  *out = ctx;
+  return GRIT_OK;
+}
+
+void grit_ctx_destroy(grit_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  if (ctx->d_keys) cudaFree(ctx->d_keys);
+  if (ctx->d_vals) cudaFree(ctx->d_vals);
+  if (ctx->d_status) cudaFree(ctx->d_status);
+  if (ctx->d_tables) cudaFree(ctx->d_tables);
+  if (ctx->d_cnt) cudaFree(ctx->d_cnt);
+  if (ctx->h_cnt) cudaFreeHost(ctx->h_cnt);
+  if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+  if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+  if (ctx->stream) cudaStreamDestroy(ctx->stream);
+  if (ctx->h2d) cudaStreamDestroy(ctx->h2d);
+  if (ctx->d2h) cudaStreamDestroy(ctx->d2h);
+  delete ctx;
+}
+
+uint64_t grit_ctx_launches(const grit_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int grit_analyze_pages(grit_ctx* ctx, const void* d_image, uint64_t n_pages, uint32_t* d_crc, uint64_t* d_hash,
+                       uint32_t* d_ref, void* stream, char* err, size_t errlen) {
+  if (int rc = enter(ctx, err, errlen)) return rc;
+  if (int rc = check_pages(n_pages, d_image, err, errlen)) return rc;
+  if (n_pages && (!d_image || !d_crc || !d_hash || !d_ref)) return fail(err, errlen, GRIT_EINVAL, "null buffer");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  GRIT_CUDA(launch_analyze(ctx->geom, ctx->d_tables, d_image, n_pages, d_crc, d_hash, d_ref, pick(ctx, stream)));
+  ctx->launches++;
+  return GRIT_OK;
+}
+
+int grit_dedup_pages(grit_ctx* ctx, uint64_t n_pages, const uint32_t* d_crc, const uint64_t* d_hash, uint32_t* d_ref,
+                     const grit_table* parent, const grit_table* peers, uint32_t n_peers, void* stream, char* err,
+                     size_t errlen) {
+  if (int rc = enter(ctx, err, errlen)) return rc;
+  if (n_pages > GRIT_MAX_PAGES) return fail(err, errlen, GRIT_EINVAL, "n_pages too large");
+  if (n_pages && (!d_crc || !d_hash || !d_ref)) return fail(err, errlen, GRIT_EINVAL, "null buffer");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  return dedup_async(ctx, n_pages, d_crc, d_hash, d_ref, parent, peers, n_peers, pick(ctx, stream), err, errlen);
+}
+
+int grit_compact_pages(grit_ctx* ctx, const void* d_image, uint64_t n_pages, uint32_t* d_ref, void* d_packed,
+                       uint64_t capacity_pages, uint64_t slot_base, uint64_t* n_stored, void* stream, char* err,
+                       size_t errlen) {
+  if (int rc = enter(ctx, err, errlen)) return rc;
+  if (int rc = check_pages(n_pages, d_image, err, errlen)) return rc;
+  if (int rc = check_pages(0, d_packed, err, errlen)) return rc;
+  if (n_pages && (!d_image || !d_ref || (!d_packed && capacity_pages))) return fail(err, errlen, GRIT_EINVAL, "null buffer");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  cudaStream_t s = pick(ctx, stream);
+  if (int rc = reset_counters(ctx, s, err, errlen)) return rc;
+  if (int rc = compact_async(ctx, d_image, n_pages, d_ref, d_packed, capacity_pages, slot_base, s, err, errlen)) return rc;
+  if (int rc = read_counters(ctx, s, err, errlen)) return rc;
+  if (n_stored) *n_stored = ctx->h_cnt->n_stored;
+  if (ctx->h_cnt->overflow)
+    return fail(err, errlen, GRIT_EINVAL, "packed buffer too small: %llu pages did not fit capacity %llu",
+                (unsigned long long)ctx->h_cnt->overflow, (unsigned long long)capacity_pages);
+  return GRIT_OK;
+}
+
+int grit_pack_buffer(grit_ctx* ctx, const void* d_image, uint64_t n_pages, const grit_table* parent,
+                     const grit_table* peers, uint32_t n_peers, void* d_packed, uint64_t capacity_pages, uint32_t* d_ref,
+                     uint32_t* d_crc, uint64_t* d_hash, grit_pack_stats* stats, void* stream, char* err, size_t errlen) {
+  if (int rc = enter(ctx, err, errlen)) return rc;
+  if (int rc = check_pages(n_pages, d_image, err, errlen)) return rc;
+  if (int rc = check_pages(0, d_packed, err, errlen)) return rc;
+  if (n_pages && (!d_image || !d_ref || !d_crc || !d_hash || (!d_packed && capacity_pages)))
+    return fail(err, errlen, GRIT_EINVAL, "null buffer");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  cudaStream_t s = pick(ctx, stream);
+  if (int rc = reset_counters(ctx, s, err, errlen)) return rc;
+  GRIT_CUDA(cudaEventRecord(ctx->ev0, s));
+  GRIT_CUDA(launch_analyze(ctx->geom, ctx->d_tables, d_image, n_pages, d_crc, d_hash, d_ref, s));
+  ctx->launches++;
+  if (int rc = dedup_async(ctx, n_pages, d_crc, d_hash, d_ref, parent, peers, n_peers, s, err, errlen)) return rc;
+  if (int rc = compact_async(ctx, d_image, n_pages, d_ref, d_packed, capacity_pages, 0, s, err, errlen)) return rc;
+  GRIT_CUDA(cudaEventRecord(ctx->ev1, s));
+  if (int rc = read_counters(ctx, s, err, errlen)) return rc;
+  const DevCounters& c = *ctx->h_cnt;
+  if (stats) {
+    stats->n_pages = n_pages;
+    stats->n_zero = c.kind[0];
+    stats->n_data = c.kind[1];
+    stats->n_dup = c.kind[2];
+    stats->n_parent = c.kind[3];
+    stats->n_peer = c.kind[4];
+    float ms = 0;
+    cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+    stats->gpu_ms = ms;
+  }
+  if (c.overflow)
+    return fail(err, errlen, GRIT_EINVAL, "packed buffer too small: %llu pages did not fit capacity %llu",
+                (unsigned long long)c.overflow, (unsigned long long)capacity_pages);
+  return GRIT_OK;
+}
+
+int grit_restore_buffer(grit_ctx* ctx, const void* d_packed, uint64_t n_slots, const uint32_t* d_ref,
+                        const uint32_t* d_crc, uint64_t n_pages, const void* d_parent_image, uint64_t parent_pages,
+                        const void* const* d_peer_images, const uint64_t* peer_pages, uint32_t n_peers, void* d_out,
+                        int verify, grit_restore_stats* stats, void* stream, char* err, size_t errlen) {
+  if (int rc = enter(ctx, err, errlen)) return rc;
+  if (int rc = check_pages(n_pages, d_out, err, errlen)) return rc;
+  if (int rc = check_pages(0, d_packed, err, errlen)) return rc;
+  if (n_peers > GRIT_MAX_PEERS) return fail(err, errlen, GRIT_EINVAL, "n_peers %u > %u", n_peers, GRIT_MAX_PEERS);
+  if (n_pages && (!d_ref || !d_out || (verify && !d_crc))) return fail(err, errlen, GRIT_EINVAL, "null buffer");
+  PeerImages imgs{};
+  imgs.parent = static_cast<const unsigned char*>(d_parent_image);
+  imgs.parent_pages = d_parent_image ? parent_pages : 0;
+  imgs.n_peers = n_peers;
+  for (uint32_t r = 0; r < n_peers; r++) {
+    imgs.peer[r] = static_cast<const unsigned char*>(d_peer_images ? d_peer_images[r] : nullptr);
+    imgs.peer_pages[r] = (imgs.peer[r] && peer_pages) ? peer_pages[r] : 0;
+  }
+  std::lock_guard<std::mutex> g(ctx->mu);
+  cudaStream_t s = pick(ctx, stream);
+  if (int rc = reset_counters(ctx, s, err, errlen)) return rc;
+  GRIT_CUDA(cudaEventRecord(ctx->ev0, s));
+  GRIT_CUDA(launch_restore(ctx->geom, ctx->d_tables, d_packed, n_slots, d_ref, d_crc, n_pages, 0, n_pages, imgs, d_out, verify,
+                           ctx->d_cnt, s));
+  ctx->launches++;
+  GRIT_CUDA(cudaEventRecord(ctx->ev1, s));
+  if (int rc = read_counters(ctx, s, err, errlen)) return rc;
+  const DevCounters& c = *ctx->h_cnt;
+  if (stats) {
+    stats->n_pages = n_pages;
+    stats->n_bad = c.n_bad;
+    stats->first_bad = c.first_bad;
+    float ms = 0;
+    cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+    stats->gpu_ms = ms;
+  }
+  if (c.n_bad)
+    return fail(err, errlen, GRIT_ECRC, "restore: %llu page(s) failed CRC-32C or had a bad reference, first page %llu",
+                (unsigned long long)c.n_bad, (unsigned long long)c.first_bad);
+  return GRIT_OK;
+}
+
+int grit_synth_image(grit_ctx* ctx, void* d_image, uint64_t n_pages, uint64_t page_base, uint64_t seed,
+                     uint32_t pct_zero, uint32_t pct_dup, uint32_t dup_pool, void* stream, char* err, size_t errlen) {
+  if (int rc = enter(ctx, err, errlen)) return rc;
+  if (int rc = check_pages(0, d_image, err, errlen)) return rc;
+  std::lock_guard<std::mutex> g(ctx->mu);
+  GRIT_CUDA(launch_synth(ctx->geom, d_image, n_pages, page_base, seed, pct_zero, pct_dup, dup_pool, pick(ctx, stream)));
+  ctx->launches++;
+  return GRIT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,59 @@
+// grit_ctx: per-device state behind the C ABI (include/gritpack.h).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+
+#include "../../include/gritpack.h"
+#include "kernels.h"
+
+struct grit_ctx {
+  int device = -1;
+  grit::LaunchGeom geom{};
+  cudaStream_t stream = nullptr;  // kernels
+  cudaStream_t h2d = nullptr;     // host pipeline copy-in
+  cudaStream_t d2h = nullptr;     // host pipeline copy-out
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  grit::Gf2Tables* d_tables = nullptr;
+  grit::DevCounters* d_cnt = nullptr;
+  grit::DevCounters* h_cnt = nullptr;  // pinned mirror
+  // scratch, grown on demand and kept for the life of the context
+  unsigned long long* d_keys = nullptr;
+  uint32_t* d_vals = nullptr;
+  uint64_t table_cap = 0;
+  unsigned long long* d_status = nullptr;
+  uint64_t status_cap = 0;
+  uint64_t launches = 0;
+  std::mutex mu;
+};
+
+namespace grit {
+
+inline int fail(char* err, size_t errlen, int code, const char* fmt, ...) {
+  if (err && errlen) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(err, errlen, fmt, ap);
+    va_end(ap);
+  }
+  return code;
+}
+
+#define GRIT_CUDA(call)                                                                         \
+  do {                                                                                          \
+    cudaError_t e_ = (call);                                                                    \
+    if (e_ != cudaSuccess)                                                                      \
+      return grit::fail(err, errlen, GRIT_ECUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e_), \
+                        __FILE__, __LINE__);                                                    \
+  } while (0)
+
+// internal stage helpers shared by api.cu and hostpipe.cu (all asynchronous on s)
+int ensure_table(grit_ctx* ctx, uint64_t n_items, DedupTable* t, char* err, size_t errlen);
+int ensure_status(grit_ctx* ctx, uint64_t n_pages, char* err, size_t errlen);
+int reset_counters(grit_ctx* ctx, cudaStream_t s, char* err, size_t errlen);
+int read_counters(grit_ctx* ctx, cudaStream_t s, char* err, size_t errlen);  // syncs s
+
+}  // namespace grit

@@ -1,0 +1,777 @@
+// Directory level of the C ABI: the drop-in for TransferData.
+//
+//   grit_pack_dir    <- copy.TransferData in the upload direction
+//                       (pkg/gritagent/checkpoint/checkpoint.go:20 -> copy.go:17-64)
+//   grit_restore_dir <- copy.TransferData in the download direction
+//                       (pkg/gritagent/restore/restore.go:16 -> copy.go:17-64)
+//
+// The reference mirrors the tree file by file (copy.go:66-90).  Here the tree
+// becomes one page stream -- every regular file, in filepath.WalkDir order
+// (copy.go:23), padded with zeros to a 4 KiB multiple -- that goes through the
+// GPU pack pipeline; the PV receives
+//     pages.bin          the pages that had to be stored, in slot order
+//     pagemap.bin        u32 ref[n_pages] then u32 crc32c[n_pages]
+//     hashes.bin         u64 hash64[n_pages]   (input of the next incremental pack)
+//     gritpack.manifest  tree layout + sizes + checksums, written last (rename)
+// and restore rebuilds paths, bytes and mode bits exactly (copy.go:36,84-89).
+#include <dirent.h>
+#include <errno.h>
+#include <fcntl.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+#include <algorithm>
+#include <chrono>
+#include <condition_variable>
+#include <cstring>
+#include <deque>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "hostpipe.h"
+
+using namespace grit;
+
+namespace {
+
+constexpr char kMagic[8] = {'G', 'R', 'I', 'T', 'P', 'A', 'K', '1'};
+constexpr uint32_t kFormatVersion = 1;
+const char* const kManifest = "gritpack.manifest";
+
+struct Entry {
+  uint8_t type;  // 0 directory, 1 regular file
+  uint32_t mode;
+  uint64_t size, first_page;
+  std::string path;  // relative to the root
+  uint64_t pages() const { return (size + kPage - 1) / kPage; }
+};
+
+struct Manifest {
+  std::vector<Entry> entries;
+  uint64_t n_pages = 0, n_slots = 0, bytes_logical = 0;
+  uint32_t pagemap_crc = 0, hashes_crc = 0;
+  std::string parent;
+};
+
+std::string errno_msg(const char* op, const std::string& path) {
+  return std::string(op) + " " + path + ": " + strerror(errno);
+}
+
+double now_s() {
+  return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+// os.MkdirAll(path, os.ModePerm), copy.go:36
+int mkdir_all(const std::string& path) {
+  struct stat st;
+  if (stat(path.c_str(), &st) == 0) return S_ISDIR(st.st_mode) ? 0 : (errno = ENOTDIR, -1);
+  const size_t slash = path.find_last_of('/');
+  if (slash != std::string::npos && slash > 0 && mkdir_all(path.substr(0, slash)) != 0) return -1;
+  if (mkdir(path.c_str(), 0777) != 0 && errno != EEXIST) return -1;
+  return 0;
+}
+
+// filepath.WalkDir order (copy.go:23): a directory, then its entries sorted by name.
+// A symlink is followed like os.Open does (copy.go:67); anything that is then
+// neither a regular file nor a directory is refused.
+int walk(const std::string& root, const std::string& rel, std::vector<Entry>* out, std::string* msg) {
+  const std::string dir = rel.empty() ? root : root + "/" + rel;
+  DIR* d = opendir(dir.c_str());
+  if (!d) return *msg = errno_msg("open", dir), GRIT_EIO;
+  std::vector<std::string> names;
+  while (struct dirent* e = readdir(d))
+    if (strcmp(e->d_name, ".") && strcmp(e->d_name, "..")) names.emplace_back(e->d_name);
+  closedir(d);
+  std::sort(names.begin(), names.end());
+  for (const auto& n : names) {
+    const std::string r = rel.empty() ? n : rel + "/" + n, full = root + "/" + r;
+    struct stat lst, st;
+    if (lstat(full.c_str(), &lst) != 0) return *msg = errno_msg("lstat", full), GRIT_EIO;
+    if (S_ISDIR(lst.st_mode)) {
+      out->push_back({0, (uint32_t)(lst.st_mode & 07777), 0, 0, r});
+      if (int rc = walk(root, r, out, msg)) return rc;
+      continue;
+    }
+    if (stat(full.c_str(), &st) != 0) return *msg = errno_msg("stat", full), GRIT_EIO;
+    if (!S_ISREG(st.st_mode)) return *msg = full + ": not a regular file or directory", GRIT_EINVAL;
+    out->push_back({1, (uint32_t)(st.st_mode & 07777), (uint64_t)st.st_size, 0, r});
+  }
+  return GRIT_OK;
+}
+
+// ---- little-endian (de)serialisation of the manifest
+void put(std::string* b, const void* p, size_t n) { b->append(static_cast<const char*>(p), n); }
+template <class T>
+void put(std::string* b, T v) {
+  put(b, &v, sizeof v);
+}
+struct Reader {
+  const std::string& b;
+  size_t off = 0;
+  bool ok = true;
+  template <class T>
+  T get() {
+    T v{};
+    if (off + sizeof v > b.size()) return ok = false, v;
+    memcpy(&v, b.data() + off, sizeof v);
+    off += sizeof v;
+    return v;
+  }
+  std::string str(size_t n) {
+    if (off + n > b.size()) return ok = false, std::string();
+    std::string s = b.substr(off, n);
+    off += n;
+    return s;
+  }
+};
+
+std::string encode_manifest(const Manifest& m) {
+  std::string b;
+  put(&b, kMagic, 8);
+  put<uint32_t>(&b, kFormatVersion);
+  put<uint32_t>(&b, (uint32_t)m.entries.size());
+  put<uint64_t>(&b, m.n_pages);
+  put<uint64_t>(&b, m.n_slots);
+  put<uint64_t>(&b, m.bytes_logical);
+  put<uint32_t>(&b, m.pagemap_crc);
+  put<uint32_t>(&b, m.hashes_crc);
+  put<uint32_t>(&b, (uint32_t)m.parent.size());
+  put(&b, m.parent.data(), m.parent.size());
+  for (const auto& e : m.entries) {
+    put<uint8_t>(&b, e.type);
+    put<uint32_t>(&b, e.mode);
+    put<uint64_t>(&b, e.size);
+    put<uint64_t>(&b, e.first_page);
+    put<uint32_t>(&b, (uint32_t)e.path.size());
+    put(&b, e.path.data(), e.path.size());
+  }
+  put<uint32_t>(&b, grit_crc32c(0, b.data(), b.size()));
+  return b;
+}
+
+int read_file(const std::string& path, std::string* out, std::string* msg) {
+  const int fd = open(path.c_str(), O_RDONLY | O_CLOEXEC);
+  if (fd < 0) return *msg = errno_msg("open", path), GRIT_EIO;
+  struct stat st;
+  if (fstat(fd, &st) != 0) {
+    *msg = errno_msg("stat", path);
+    close(fd);
+    return GRIT_EIO;
+  }
+  out->resize((size_t)st.st_size);
+  size_t off = 0;
+  while (off < out->size()) {
+    const ssize_t n = pread(fd, &(*out)[off], out->size() - off, (off_t)off);
+    if (n <= 0) {
+      if (n < 0 && errno == EINTR) continue;
+      *msg = errno_msg("read", path);
+      close(fd);
+      return GRIT_EIO;
+    }
+    off += (size_t)n;
+  }
+  close(fd);
+  return GRIT_OK;
+}
+
+int write_file(const std::string& path, const void* data, size_t len, std::string* msg) {
+  const int fd = open(path.c_str(), O_WRONLY | O_CREAT | O_TRUNC | O_CLOEXEC, 0666);
+  if (fd < 0) return *msg = errno_msg("open", path), GRIT_EIO;
+  const char* p = static_cast<const char*>(data);
+  size_t off = 0;
+  while (off < len) {
+    const ssize_t n = write(fd, p + off, len - off);
+    if (n < 0) {
+      if (errno == EINTR) continue;
+      *msg = errno_msg("write", path);
+      close(fd);
+      return GRIT_EIO;
+    }
+    off += (size_t)n;
+  }
+  if (fsync(fd) != 0 || close(fd) != 0) return *msg = errno_msg("fsync", path), GRIT_EIO;
+  return GRIT_OK;
+}
+
+bool has_manifest(const std::string& dir) {
+  struct stat st;
+  return stat((dir + "/" + kManifest).c_str(), &st) == 0 && S_ISREG(st.st_mode);
+}
+
+int load_manifest(const std::string& dir, Manifest* m, std::string* msg) {
+  std::string b;
+  if (int rc = read_file(dir + "/" + kManifest, &b, msg)) return rc;
+  if (b.size() < 8 + 4 * 2 + 8 * 3 + 4 * 3 + 4 || memcmp(b.data(), kMagic, 8))
+    return *msg = dir + ": not a gritpack manifest", GRIT_EFORMAT;
+  uint32_t want;
+  memcpy(&want, b.data() + b.size() - 4, 4);
+  if (grit_crc32c(0, b.data(), b.size() - 4) != want) return *msg = dir + ": manifest checksum mismatch", GRIT_EFORMAT;
+  Reader r{b, 8};
+  if (r.get<uint32_t>() != kFormatVersion) return *msg = dir + ": unknown manifest version", GRIT_EFORMAT;
+  const uint32_t n_entries = r.get<uint32_t>();
+  m->n_pages = r.get<uint64_t>();
+  m->n_slots = r.get<uint64_t>();
+  m->bytes_logical = r.get<uint64_t>();
+  m->pagemap_crc = r.get<uint32_t>();
+  m->hashes_crc = r.get<uint32_t>();
+  m->parent = r.str(r.get<uint32_t>());
+  for (uint32_t i = 0; i < n_entries && r.ok; i++) {
+    Entry e;
+    e.type = r.get<uint8_t>();
+    e.mode = r.get<uint32_t>();
+    e.size = r.get<uint64_t>();
+    e.first_page = r.get<uint64_t>();
+    e.path = r.str(r.get<uint32_t>());
+    if (e.path.empty() || e.path[0] == '/' || e.path.find("..") != std::string::npos)
+      return *msg = dir + ": manifest holds an unsafe path", GRIT_EFORMAT;
+    m->entries.push_back(std::move(e));
+  }
+  if (!r.ok || r.off + 4 != b.size() || m->n_pages > GRIT_MAX_PAGES) return *msg = dir + ": truncated manifest", GRIT_EFORMAT;
+  return GRIT_OK;
+}
+
+// per-page arrays of a packed directory
+int load_pagemap(const std::string& dir, const Manifest& m, std::vector<uint32_t>* ref, std::vector<uint32_t>* crc,
+                 std::string* msg) {
+  std::string b;
+  if (int rc = read_file(dir + "/pagemap.bin", &b, msg)) return rc;
+  if (b.size() != m.n_pages * 8 || grit_crc32c(0, b.data(), b.size()) != m.pagemap_crc)
+    return *msg = dir + "/pagemap.bin: size or checksum mismatch", GRIT_EFORMAT;
+  ref->resize(m.n_pages);
+  crc->resize(m.n_pages);
+  memcpy(ref->data(), b.data(), m.n_pages * 4);
+  memcpy(crc->data(), b.data() + m.n_pages * 4, m.n_pages * 4);
+  return GRIT_OK;
+}
+
+int load_hashes(const std::string& dir, const Manifest& m, std::vector<uint64_t>* hash, std::string* msg) {
+  std::string b;
+  if (int rc = read_file(dir + "/hashes.bin", &b, msg)) return rc;
+  if (b.size() != m.n_pages * 8 || grit_crc32c(0, b.data(), b.size()) != m.hashes_crc)
+    return *msg = dir + "/hashes.bin: size or checksum mismatch", GRIT_EFORMAT;
+  hash->resize(m.n_pages);
+  memcpy(hash->data(), b.data(), b.size());
+  return GRIT_OK;
+}
+
+// One contiguous piece of file I/O between a file and a staging buffer.
+struct Piece {
+  const Entry* e;
+  uint64_t file_off, len;
+  char* buf;
+};
+
+// the pieces of page range [p0, p1) of the stream, each at most 8 MiB
+void pieces_for(const std::vector<const Entry*>& files, uint64_t p0, uint64_t p1, char* buf, std::vector<Piece>* out) {
+  auto it = std::upper_bound(files.begin(), files.end(), p0,
+                             [](uint64_t p, const Entry* e) { return p < e->first_page + e->pages(); });
+  for (; it != files.end() && (*it)->first_page < p1; ++it) {
+    const Entry* e = *it;
+    const uint64_t a = std::max(p0, e->first_page), b = std::min(p1, e->first_page + e->pages());
+    uint64_t off = (a - e->first_page) * kPage;
+    const uint64_t end = std::min<uint64_t>(e->size, (b - e->first_page) * kPage);
+    char* dst = buf + (a - p0) * kPage;
+    while (off < end) {
+      const uint64_t n = std::min<uint64_t>(end - off, 8ull << 20);
+      out->push_back({e, off, n, dst});
+      off += n;
+      dst += n;
+    }
+  }
+}
+
+// run fn over the pieces on `threads` threads; first error wins
+template <class Fn>
+int for_pieces(const std::vector<Piece>& ps, unsigned threads, std::string* msg, Fn fn) {
+  if (ps.empty()) return GRIT_OK;
+  threads = std::max(1u, std::min<unsigned>(threads, (unsigned)ps.size()));
+  std::vector<std::string> errs(threads);
+  std::vector<std::thread> th;
+  for (unsigned t = 0; t < threads; t++)
+    th.emplace_back([&, t] {
+      for (size_t i = t; i < ps.size() && errs[t].empty(); i += threads) fn(ps[i], &errs[t]);
+    });
+  for (auto& x : th) x.join();
+  for (auto& e : errs)
+    if (!e.empty()) return *msg = e, GRIT_EIO;
+  return GRIT_OK;
+}
+
+void read_piece(const std::string& root, const Piece& p, std::string* err) {
+  const std::string path = root + "/" + p.e->path;
+  const int fd = open(path.c_str(), O_RDONLY | O_CLOEXEC);
+  if (fd < 0) return void(*err = errno_msg("open", path));
+  uint64_t done = 0;
+  while (done < p.len) {
+    const ssize_t n = pread(fd, p.buf + done, p.len - done, (off_t)(p.file_off + done));
+    if (n < 0 && errno == EINTR) continue;
+    if (n <= 0) {  // the file shrank under us: the image would not be the one the manifest describes
+      *err = n < 0 ? errno_msg("read", path) : path + ": file changed while packing";
+      break;
+    }
+    done += (uint64_t)n;
+  }
+  close(fd);
+}
+
+void write_piece(const std::string& root, const Piece& p, std::string* err) {
+  const std::string path = root + "/" + p.e->path;
+  const int fd = open(path.c_str(), O_WRONLY | O_CLOEXEC);
+  if (fd < 0) return void(*err = errno_msg("open", path));
+  uint64_t done = 0;
+  while (done < p.len) {
+    const ssize_t n = pwrite(fd, p.buf + done, p.len - done, (off_t)(p.file_off + done));
+    if (n < 0 && errno == EINTR) continue;
+    if (n <= 0) {
+      *err = errno_msg("write", path);
+      break;
+    }
+    done += (uint64_t)n;
+  }
+  close(fd);
+}
+
+struct Opts {
+  int device = 0;
+  bool verify = true;
+  unsigned io_threads = 4;
+  uint64_t chunk_pages = (64ull << 20) / kPage;
+  std::string parent;
+};
+
+Opts read_opts(const grit_opts* o) {
+  Opts r;
+  if (!o) return r;
+  r.device = o->device;
+  r.verify = o->verify != 0;
+  if (o->io_threads) r.io_threads = o->io_threads;
+  if (o->chunk_bytes >= (1u << 20)) r.chunk_pages = o->chunk_bytes / kPage;
+  if (o->parent_dir) r.parent = o->parent_dir;
+  return r;
+}
+
+struct CtxGuard {
+  grit_ctx* ctx = nullptr;
+  ~CtxGuard() { grit_ctx_destroy(ctx); }
+};
+
+// Restores the whole image of a packed directory into device memory (used for
+// parents of incremental checkpoints).  Follows the parent chain recursively.
+int image_to_device(grit_ctx* ctx, const std::string& dir, int verify, void** d_image, uint64_t* n_pages, int depth,
+                    grit_stats* stats, std::string* msg);
+
+std::string resolve_parent(const std::string& child_dir, const std::string& parent) {
+  if (has_manifest(parent)) return parent;
+  // the PV may be mounted elsewhere at restore time: try the sibling of the same name
+  const size_t s1 = parent.find_last_not_of('/');
+  const size_t s0 = parent.find_last_of('/', s1);
+  const std::string base = parent.substr(s0 == std::string::npos ? 0 : s0 + 1, s1 - (s0 == std::string::npos ? 0 : s0 + 1) + 1);
+  const size_t c = child_dir.find_last_of('/', child_dir.find_last_not_of('/'));
+  const std::string sib = (c == std::string::npos ? std::string(".") : child_dir.substr(0, c)) + "/" + base;
+  return has_manifest(sib) ? sib : parent;
+}
+
+int image_to_device(grit_ctx* ctx, const std::string& dir, int verify, void** d_image, uint64_t* n_pages, int depth,
+                    grit_stats* stats, std::string* msg) {
+  if (depth > 64) return *msg = "parent chain too deep", GRIT_EFORMAT;
+  Manifest m;
+  if (int rc = load_manifest(dir, &m, msg)) return rc;
+  std::vector<uint32_t> ref, crc;
+  if (int rc = load_pagemap(dir, m, &ref, &crc, msg)) return rc;
+  void* d_parent = nullptr;
+  uint64_t parent_pages = 0;
+  if (!m.parent.empty())
+    if (int rc = image_to_device(ctx, resolve_parent(dir, m.parent), verify, &d_parent, &parent_pages, depth + 1, stats, msg))
+      return rc;
+  char err[512] = "";
+  const size_t errlen = sizeof err;
+  void *d_packed = nullptr, *d_out = nullptr;
+  uint32_t *d_ref = nullptr, *d_crc = nullptr;
+  auto cleanup = [&] {
+    cudaFree(d_packed);
+    cudaFree(d_ref);
+    cudaFree(d_crc);
+    cudaFree(d_parent);
+  };
+  auto body = [&]() -> int {
+    GRIT_CUDA(cudaMalloc(&d_packed, std::max<uint64_t>(m.n_slots, 1) * kPage));
+    GRIT_CUDA(cudaMalloc(&d_out, std::max<uint64_t>(m.n_pages, 1) * kPage));
+    GRIT_CUDA(cudaMalloc(&d_ref, std::max<uint64_t>(m.n_pages, 1) * 4));
+    GRIT_CUDA(cudaMalloc(&d_crc, std::max<uint64_t>(m.n_pages, 1) * 4));
+    // pages.bin -> device through a pinned bounce buffer
+    const std::string pages = dir + "/pages.bin";
+    const int fd = open(pages.c_str(), O_RDONLY | O_CLOEXEC);
+    if (fd < 0) return fail(err, errlen, GRIT_EIO, "%s", errno_msg("open", pages).c_str());
+    void* h = nullptr;
+    const uint64_t step = 32ull << 20;
+    if (cudaMallocHost(&h, step) != cudaSuccess) {
+      close(fd);
+      return fail(err, errlen, GRIT_ECUDA, "cudaMallocHost failed");
+    }
+    int rc = GRIT_OK;
+    for (uint64_t off = 0; off < m.n_slots * kPage && !rc; off += step) {
+      const uint64_t n = std::min(step, m.n_slots * kPage - off);
+      uint64_t done = 0;
+      while (done < n) {
+        const ssize_t k = pread(fd, static_cast<char*>(h) + done, n - done, (off_t)(off + done));
+        if (k < 0 && errno == EINTR) continue;
+        if (k <= 0) {
+          rc = fail(err, errlen, GRIT_EIO, "%s: short read", pages.c_str());
+          break;
+        }
+        done += (uint64_t)k;
+      }
+      if (!rc && cudaMemcpy(static_cast<char*>(d_packed) + off, h, n, cudaMemcpyHostToDevice) != cudaSuccess)
+        rc = fail(err, errlen, GRIT_ECUDA, "H2D of %s failed", pages.c_str());
+      if (stats) stats->h2d_bytes += (double)n;
+    }
+    cudaFreeHost(h);
+    close(fd);
+    if (rc) return rc;
+    GRIT_CUDA(cudaMemcpy(d_ref, ref.data(), m.n_pages * 4, cudaMemcpyHostToDevice));
+    GRIT_CUDA(cudaMemcpy(d_crc, crc.data(), m.n_pages * 4, cudaMemcpyHostToDevice));
+    grit_restore_stats rs{};
+    rc = grit_restore_buffer(ctx, d_packed, m.n_slots, d_ref, d_crc, m.n_pages, d_parent, parent_pages, nullptr, nullptr,
+                             0, d_out, verify, &rs, nullptr, err, errlen);
+    if (stats) {
+      stats->gpu_ms += rs.gpu_ms;
+      stats->n_bad += rs.n_bad;
+    }
+    return rc;
+  };
+  const int rc = body();
+  cleanup();
+  if (rc) {
+    cudaFree(d_out);
+    *msg = dir + ": " + err;
+    return rc;
+  }
+  *d_image = d_out;
+  *n_pages = m.n_pages;
+  return GRIT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int grit_pack_dir(const char* src_dir, const char* dst_dir, const grit_opts* opts, grit_stats* stats, char* err,
+                  size_t errlen) {
+  if (!src_dir || !dst_dir) return fail(err, errlen, GRIT_EINVAL, "null directory");
+  const double t0 = now_s();
+  const Opts o = read_opts(opts);
+  const std::string src = src_dir, dst = dst_dir;
+  std::string msg;
+  grit_stats st{};
+
+  Manifest m;
+  struct stat sst;
+  if (stat(src.c_str(), &sst) != 0 || !S_ISDIR(sst.st_mode)) return fail(err, errlen, GRIT_EIO, "%s: not a directory", src_dir);
+  if (int rc = walk(src, "", &m.entries, &msg)) return fail(err, errlen, rc, "%s", msg.c_str());
+  std::vector<const Entry*> files;
+  for (auto& e : m.entries) {
+    if (e.type == 0) {
+      st.n_dirs++;
+      continue;
+    }
+    e.first_page = m.n_pages;
+    m.n_pages += e.pages();
+    m.bytes_logical += e.size;
+    st.n_files++;
+    if (e.size) files.push_back(&e);
+  }
+  if (m.n_pages > GRIT_MAX_PAGES) return fail(err, errlen, GRIT_EINVAL, "%s: image exceeds GRIT_MAX_PAGES pages", src_dir);
+
+  // previous checkpoint's per-page hashes, for incremental packs
+  std::vector<uint64_t> p_hash;
+  std::vector<uint32_t> p_ref, p_crc;
+  grit_table parent{};
+  if (!o.parent.empty()) {
+    Manifest pm;
+    if (int rc = load_manifest(o.parent, &pm, &msg)) return fail(err, errlen, rc, "parent: %s", msg.c_str());
+    if (int rc = load_pagemap(o.parent, pm, &p_ref, &p_crc, &msg)) return fail(err, errlen, rc, "parent: %s", msg.c_str());
+    if (int rc = load_hashes(o.parent, pm, &p_hash, &msg)) return fail(err, errlen, rc, "parent: %s", msg.c_str());
+    parent.hash = p_hash.data();
+    parent.crc = p_crc.data();
+    parent.n_pages = pm.n_pages;
+    m.parent = o.parent;
+  }
+
+  if (mkdir_all(dst) != 0) return fail(err, errlen, GRIT_EIO, "%s", errno_msg("mkdir", dst).c_str());
+  // a re-run (Job retry) must never leave an old manifest vouching for new, partial data
+  if (unlink((dst + "/" + kManifest).c_str()) != 0 && errno != ENOENT)
+    return fail(err, errlen, GRIT_EIO, "%s", errno_msg("unlink", dst + "/" + kManifest).c_str());
+  const std::string pages_path = dst + "/pages.bin";
+  const int pages_fd = open(pages_path.c_str(), O_WRONLY | O_CREAT | O_TRUNC | O_CLOEXEC, 0666);
+  if (pages_fd < 0) return fail(err, errlen, GRIT_EIO, "%s", errno_msg("open", pages_path).c_str());
+  struct FdGuard {
+    int fd;
+    ~FdGuard() {
+      if (fd >= 0) close(fd);
+    }
+  } pages_guard{pages_fd};
+
+  CtxGuard cg;
+  if (int rc = grit_ctx_create(o.device, &cg.ctx, err, errlen)) return rc;
+  grit_ctx* ctx = cg.ctx;
+  std::vector<uint32_t> ref(std::max<uint64_t>(m.n_pages, 1)), crc(std::max<uint64_t>(m.n_pages, 1));
+  std::vector<uint64_t> hash(std::max<uint64_t>(m.n_pages, 1));
+  grit_pack_stats ps{};
+  {
+    PackStream pk(ctx, m.n_pages, o.chunk_pages);
+    if (int rc = pk.begin(parent.n_pages ? &parent : nullptr, err, errlen)) return rc;
+    if (m.n_pages)
+      if (int rc = pk.alloc_staging(true, true, err, errlen)) return rc;
+    const uint64_t cp = pk.chunk_pages(), n_chunks = (m.n_pages + cp - 1) / cp;
+
+    // writer thread: chunk outputs -> pages.bin, in order
+    struct Job {
+      uint64_t chunk, first_slot, n_out;
+    };
+    std::mutex mu;
+    std::condition_variable cv;
+    std::deque<Job> jobs;
+    uint64_t written_chunks = 0;
+    bool stop = false;
+    std::string werr;
+    std::thread writer([&] {
+      cudaSetDevice(ctx->device);
+      for (;;) {
+        Job j;
+        {
+          std::unique_lock<std::mutex> l(mu);
+          cv.wait(l, [&] { return stop || !jobs.empty(); });
+          if (jobs.empty()) return;
+          j = jobs.front();
+          jobs.pop_front();
+        }
+        char e2[256] = "";
+        std::string local;
+        if (pk.wait_out(j.chunk, e2, sizeof e2)) local = e2;
+        const char* p = static_cast<const char*>(pk.out_buffer(j.chunk));
+        uint64_t done = 0;
+        while (local.empty() && done < j.n_out * kPage) {
+          const ssize_t n = pwrite(pages_fd, p + done, j.n_out * kPage - done, (off_t)(j.first_slot * kPage + done));
+          if (n < 0 && errno == EINTR) continue;
+          if (n <= 0) local = errno_msg("write", pages_path);
+          else done += (uint64_t)n;
+        }
+        {
+          std::lock_guard<std::mutex> l(mu);
+          if (!local.empty() && werr.empty()) werr = local;
+          written_chunks++;
+        }
+        cv.notify_all();
+      }
+    });
+    auto stop_writer = [&] {
+      {
+        std::lock_guard<std::mutex> l(mu);
+        stop = true;
+      }
+      cv.notify_all();
+      if (writer.joinable()) writer.join();
+    };
+    int rc = GRIT_OK;
+    for (uint64_t i = 0; i <= n_chunks && !rc; i++) {
+      if (i < n_chunks) {
+        const uint64_t p0 = i * cp, p1 = std::min(m.n_pages, p0 + cp);
+        if ((rc = pk.wait_in_free(i, err, errlen))) break;
+        char* buf = static_cast<char*>(pk.in_buffer(i));
+        memset(buf, 0, (p1 - p0) * kPage);  // tails of files shorter than a page multiple read as zeros
+        std::vector<Piece> pieces;
+        pieces_for(files, p0, p1, buf, &pieces);
+        if ((rc = for_pieces(pieces, o.io_threads, &msg, [&](const Piece& p, std::string* e) { read_piece(src, p, e); }))) {
+          fail(err, errlen, rc, "%s", msg.c_str());
+          break;
+        }
+        if ((rc = pk.submit(i, buf, p1 - p0, err, errlen))) break;
+      }
+      if (i >= 1) {
+        const uint64_t j = i - 1;
+        if (j >= (uint64_t)kPipeDepth) {  // out_buffer(j) must have been written out
+          std::unique_lock<std::mutex> l(mu);
+          cv.wait(l, [&] { return written_chunks + kPipeDepth > j; });
+        }
+        Job job{j, 0, 0};
+        if ((rc = pk.collect(j, pk.out_buffer(j), &job.first_slot, &job.n_out, err, errlen))) break;
+        {
+          std::lock_guard<std::mutex> l(mu);
+          jobs.push_back(job);
+        }
+        cv.notify_all();
+      }
+    }
+    if (!rc) {
+      std::unique_lock<std::mutex> l(mu);
+      cv.wait(l, [&] { return written_chunks == n_chunks; });
+    }
+    stop_writer();
+    if (!rc && !werr.empty()) rc = fail(err, errlen, GRIT_EIO, "%s", werr.c_str());
+    if (rc) return rc;
+    if ((rc = pk.finish(ref.data(), crc.data(), hash.data(), &ps, err, errlen))) return rc;
+    st.h2d_bytes = pk.h2d_bytes;
+    st.d2h_bytes = pk.d2h_bytes;
+  }
+  if (ps.n_peer) return fail(err, errlen, GRIT_EINVAL, "internal: peer references in a single-rank pack");
+  m.n_slots = ps.n_data;
+  if (fsync(pages_fd) != 0) return fail(err, errlen, GRIT_EIO, "%s", errno_msg("fsync", pages_path).c_str());
+
+  std::string pagemap(m.n_pages * 8, '\0');
+  memcpy(&pagemap[0], ref.data(), m.n_pages * 4);
+  memcpy(&pagemap[m.n_pages * 4], crc.data(), m.n_pages * 4);
+  m.pagemap_crc = grit_crc32c(0, pagemap.data(), pagemap.size());
+  m.hashes_crc = grit_crc32c(0, hash.data(), m.n_pages * 8);
+  if (int rc = write_file(dst + "/pagemap.bin", pagemap.data(), pagemap.size(), &msg)) return fail(err, errlen, rc, "%s", msg.c_str());
+  if (int rc = write_file(dst + "/hashes.bin", hash.data(), m.n_pages * 8, &msg)) return fail(err, errlen, rc, "%s", msg.c_str());
+  // the manifest goes last, through a rename: its presence means the pack is complete
+  const std::string enc = encode_manifest(m), tmp = dst + "/" + kManifest + ".tmp";
+  if (int rc = write_file(tmp, enc.data(), enc.size(), &msg)) return fail(err, errlen, rc, "%s", msg.c_str());
+  if (rename(tmp.c_str(), (dst + "/" + kManifest).c_str()) != 0)
+    return fail(err, errlen, GRIT_EIO, "%s", errno_msg("rename", tmp).c_str());
+  const int dfd = open(dst.c_str(), O_RDONLY | O_DIRECTORY | O_CLOEXEC);
+  if (dfd >= 0) {
+    fsync(dfd);
+    close(dfd);
+  }
+
+  st.bytes_logical = m.bytes_logical;
+  st.bytes_stored = m.n_slots * kPage + pagemap.size() + m.n_pages * 8 + enc.size();
+  st.n_pages = ps.n_pages;
+  st.n_zero = ps.n_zero;
+  st.n_data = ps.n_data;
+  st.n_dup = ps.n_dup;
+  st.n_parent = ps.n_parent;
+  st.n_peer = ps.n_peer;
+  st.gpu_ms = ps.gpu_ms;
+  st.seconds = now_s() - t0;
+  if (stats) *stats = st;
+  return GRIT_OK;
+}
+
+int grit_restore_dir(const char* src_dir, const char* dst_dir, const grit_opts* opts, grit_stats* stats, char* err,
+                     size_t errlen) {
+  if (!src_dir || !dst_dir) return fail(err, errlen, GRIT_EINVAL, "null directory");
+  const double t0 = now_s();
+  const Opts o = read_opts(opts);
+  const std::string src = src_dir, dst = dst_dir;
+  std::string msg;
+  grit_stats st{};
+  if (!has_manifest(src))
+    return fail(err, errlen, GRIT_EFORMAT,
+                "%s holds no %s: not a complete gritpack image (a plain mirror written by the stock agent "
+                "is restored by the stock agent)",
+                src_dir, kManifest);
+  Manifest m;
+  if (int rc = load_manifest(src, &m, &msg)) return fail(err, errlen, rc, "%s", msg.c_str());
+  std::vector<uint32_t> ref, crc;
+  if (int rc = load_pagemap(src, m, &ref, &crc, &msg)) return fail(err, errlen, rc, "%s", msg.c_str());
+  for (uint64_t p = 0; p < m.n_pages; p++)
+    if (GRIT_REF_KIND(ref[p]) == GRIT_KIND_PEER)
+      return fail(err, errlen, GRIT_EFORMAT, "%s: page %llu refers to a peer rank's image", src_dir, (unsigned long long)p);
+
+  CtxGuard cg;
+  if (int rc = grit_ctx_create(o.device, &cg.ctx, err, errlen)) return rc;
+  grit_ctx* ctx = cg.ctx;
+
+  void* d_parent = nullptr;
+  uint64_t parent_pages = 0;
+  struct DevGuard {
+    void** p;
+    ~DevGuard() { cudaFree(*p); }
+  } parent_guard{&d_parent};
+  if (!m.parent.empty()) {
+    if (int rc = image_to_device(ctx, resolve_parent(src, m.parent), o.verify, &d_parent, &parent_pages, 0, &st, &msg))
+      return fail(err, errlen, rc, "parent: %s", msg.c_str());
+  }
+
+  // tree skeleton: directories 0777 & ~umask (copy.go:36), files created and sized
+  if (mkdir_all(dst) != 0) return fail(err, errlen, GRIT_EIO, "%s", errno_msg("mkdir", dst).c_str());
+  std::vector<const Entry*> files;
+  for (const auto& e : m.entries) {
+    const std::string path = dst + "/" + e.path;
+    if (e.type == 0) {
+      st.n_dirs++;
+      if (mkdir_all(path) != 0) return fail(err, errlen, GRIT_EIO, "%s", errno_msg("mkdir", path).c_str());
+      continue;
+    }
+    st.n_files++;
+    const int fd = open(path.c_str(), O_WRONLY | O_CREAT | O_TRUNC | O_CLOEXEC, 0666);  // os.Create, copy.go:73
+    if (fd < 0) return fail(err, errlen, GRIT_EIO, "%s", errno_msg("open", path).c_str());
+    const int trc = ftruncate(fd, (off_t)e.size);
+    close(fd);
+    if (trc != 0) return fail(err, errlen, GRIT_EIO, "%s", errno_msg("truncate", path).c_str());
+    if (e.size) files.push_back(&e);
+  }
+
+  const std::string pages_path = src + "/pages.bin";
+  const int pages_fd = open(pages_path.c_str(), O_RDONLY | O_CLOEXEC);
+  if (pages_fd < 0) return fail(err, errlen, GRIT_EIO, "%s", errno_msg("open", pages_path).c_str());
+  struct FdGuard {
+    int fd;
+    ~FdGuard() { close(fd); }
+  } pages_guard{pages_fd};
+  struct stat pst;
+  if (fstat(pages_fd, &pst) != 0 || (uint64_t)pst.st_size != m.n_slots * kPage)
+    return fail(err, errlen, GRIT_EFORMAT, "%s: size does not match the manifest", pages_path.c_str());
+
+  RestoreIO io;
+  io.read_packed = [&](uint64_t s0, uint64_t n, void* dstbuf) -> int {
+    uint64_t done = 0;
+    while (done < n * kPage) {
+      const ssize_t k = pread(pages_fd, static_cast<char*>(dstbuf) + done, n * kPage - done, (off_t)(s0 * kPage + done));
+      if (k < 0 && errno == EINTR) continue;
+      if (k <= 0) return GRIT_EIO;
+      done += (uint64_t)k;
+    }
+    return 0;
+  };
+  io.write_out = [&](uint64_t p0, uint64_t p1, const void* srcbuf) -> int {
+    std::vector<Piece> pieces;
+    pieces_for(files, p0, p1, const_cast<char*>(static_cast<const char*>(srcbuf)), &pieces);
+    return for_pieces(pieces, o.io_threads, &msg, [&](const Piece& p, std::string* e) { write_piece(dst, p, e); });
+  };
+  grit_restore_stats rs{};
+  {
+    std::lock_guard<std::mutex> g(ctx->mu);
+    const int rc = restore_stream(ctx, io, m.n_slots, ref.data(), crc.data(), m.n_pages, d_parent, parent_pages, true,
+                                  o.verify, o.chunk_pages, &rs, &st.h2d_bytes, &st.d2h_bytes, err, errlen);
+    st.n_bad += rs.n_bad;
+    if (rc) {
+      if (!msg.empty() && err && errlen) snprintf(err, errlen, "%s", msg.c_str());
+      if (stats) *stats = st;
+      return rc;
+    }
+  }
+  // os.Chmod(dstFile, info.Mode()), copy.go:84-89; then make the bytes durable before
+  // the caller writes the sentinel that patched containerd polls for (restore.go:20)
+  for (const auto& e : m.entries) {
+    if (e.type != 1) continue;
+    const std::string path = dst + "/" + e.path;
+    const int fd = open(path.c_str(), O_WRONLY | O_CLOEXEC);
+    if (fd < 0) return fail(err, errlen, GRIT_EIO, "%s", errno_msg("open", path).c_str());
+    const int r1 = fsync(fd), r2 = fchmod(fd, e.mode);
+    close(fd);
+    if (r1 != 0 || r2 != 0) return fail(err, errlen, GRIT_EIO, "%s", errno_msg("chmod", path).c_str());
+  }
+
+  st.bytes_logical = m.bytes_logical;
+  st.bytes_stored = m.n_slots * kPage;
+  st.n_pages = m.n_pages;
+  for (uint64_t p = 0; p < m.n_pages; p++) {
+    switch (GRIT_REF_KIND(ref[p])) {
+      case GRIT_KIND_ZERO: st.n_zero++; break;
+      case GRIT_KIND_DATA: st.n_data++; break;
+      case GRIT_KIND_DUP: st.n_dup++; break;
+      case GRIT_KIND_PARENT: st.n_parent++; break;
+      default: break;
+    }
+  }
+  st.gpu_ms += rs.gpu_ms;
+  st.seconds = now_s() - t0;
+  if (stats) *stats = st;
+  return GRIT_OK;
+}
+
+}  // extern "C"

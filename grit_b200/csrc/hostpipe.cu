@@ -1,0 +1,465 @@
+// Pinned, event-chained host<->device pipeline around the page kernels.
+// See hostpipe.h; C ABI declarations in include/gritpack.h.
+#include "hostpipe.h"
+
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+
+using namespace grit;
+
+namespace grit {
+
+bool is_pinned(const void* p) {
+  cudaPointerAttributes a{};
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return a.type == cudaMemoryTypeHost;
+}
+
+// ------------------------------------------------------------------ PackStream
+PackStream::PackStream(grit_ctx* ctx, uint64_t total_pages, uint64_t chunk_pages)
+    : ctx_(ctx), total_pages_(total_pages), chunk_pages_(std::max<uint64_t>(chunk_pages, kCompactTile)) {}
+
+PackStream::~PackStream() {
+  cudaSetDevice(ctx_->device);
+  cudaStreamSynchronize(ctx_->h2d);
+  cudaStreamSynchronize(ctx_->stream);
+  cudaStreamSynchronize(ctx_->d2h);
+  for (int b = 0; b < kPipeDepth; b++) {
+    if (d_in_[b]) cudaFree(d_in_[b]);
+    if (d_out_[b]) cudaFree(d_out_[b]);
+    if (h_in_[b]) cudaFreeHost(h_in_[b]);
+    if (h_out_[b]) cudaFreeHost(h_out_[b]);
+    if (ev_h2d_[b]) cudaEventDestroy(ev_h2d_[b]);
+    if (ev_kern_[b]) cudaEventDestroy(ev_kern_[b]);
+    if (ev_d2h_[b]) cudaEventDestroy(ev_d2h_[b]);
+  }
+  if (h_counts_) cudaFreeHost(h_counts_);
+  if (d_ref_) cudaFree(d_ref_);
+  if (d_crc_) cudaFree(d_crc_);
+  if (d_hash_) cudaFree(d_hash_);
+  if (d_parent_hash_) cudaFree(d_parent_hash_);
+  if (d_parent_crc_) cudaFree(d_parent_crc_);
+}
+
+int PackStream::begin(const grit_table* parent, char* err, size_t errlen) {
+  GRIT_CUDA(cudaSetDevice(ctx_->device));
+  if (total_pages_ > GRIT_MAX_PAGES) return fail(err, errlen, GRIT_EINVAL, "image exceeds GRIT_MAX_PAGES");
+  const size_t chunk_bytes = chunk_pages_ * kPage;
+  for (int b = 0; b < kPipeDepth; b++) {
+    GRIT_CUDA(cudaMalloc(&d_in_[b], chunk_bytes));
+    GRIT_CUDA(cudaMalloc(&d_out_[b], chunk_bytes));
+    GRIT_CUDA(cudaEventCreateWithFlags(&ev_h2d_[b], cudaEventDisableTiming));
+    GRIT_CUDA(cudaEventCreateWithFlags(&ev_kern_[b], cudaEventDisableTiming));
+    GRIT_CUDA(cudaEventCreateWithFlags(&ev_d2h_[b], cudaEventDisableTiming));
+  }
+  GRIT_CUDA(cudaMallocHost(&h_counts_, kPipeDepth * sizeof(unsigned long long)));
+  const uint64_t n = std::max<uint64_t>(total_pages_, 1);
+  GRIT_CUDA(cudaMalloc(&d_ref_, n * 4));
+  GRIT_CUDA(cudaMalloc(&d_crc_, n * 4));
+  GRIT_CUDA(cudaMalloc(&d_hash_, n * 8));
+  uint64_t items = total_pages_;
+  if (parent && parent->n_pages) {
+    if (parent->n_pages > GRIT_MAX_PAGES) return fail(err, errlen, GRIT_EINVAL, "parent exceeds GRIT_MAX_PAGES");
+    items += parent->n_pages;
+    GRIT_CUDA(cudaMalloc(&d_parent_hash_, parent->n_pages * 8));
+    GRIT_CUDA(cudaMalloc(&d_parent_crc_, parent->n_pages * 4));
+    GRIT_CUDA(cudaMemcpyAsync(d_parent_hash_, parent->hash, parent->n_pages * 8, cudaMemcpyHostToDevice, ctx_->stream));
+    GRIT_CUDA(cudaMemcpyAsync(d_parent_crc_, parent->crc, parent->n_pages * 4, cudaMemcpyHostToDevice, ctx_->stream));
+    crcs_.parent = d_parent_crc_;
+    h2d_bytes += parent->n_pages * 12.0;
+  }
+  if (int rc = ensure_table(ctx_, items, &table_, err, errlen)) return rc;
+  if (int rc = ensure_status(ctx_, chunk_pages_, err, errlen)) return rc;
+  cudaStream_t s = ctx_->stream;
+  if (int rc = reset_counters(ctx_, s, err, errlen)) return rc;
+  GRIT_CUDA(cudaMemsetAsync(table_.keys, 0, (table_.mask + 1) * sizeof(unsigned long long), s));
+  GRIT_CUDA(cudaMemsetAsync(table_.vals, 0xFF, (table_.mask + 1) * sizeof(uint32_t), s));
+  if (parent && parent->n_pages) {
+    GRIT_CUDA(launch_table_insert(ctx_->geom, table_, d_parent_hash_, nullptr, parent->n_pages, 0, 0, s));
+    ctx_->launches++;
+  }
+  return GRIT_OK;
+}
+
+int PackStream::alloc_staging(bool in, bool out, char* err, size_t errlen) {
+  for (int b = 0; b < kPipeDepth; b++) {
+    if (in && !h_in_[b]) GRIT_CUDA(cudaMallocHost(&h_in_[b], chunk_pages_ * kPage));
+    if (out && !h_out_[b]) GRIT_CUDA(cudaMallocHost(&h_out_[b], chunk_pages_ * kPage));
+  }
+  return GRIT_OK;
+}
+
+int PackStream::wait_in_free(uint64_t i, char* err, size_t errlen) {
+  if (i >= (uint64_t)kPipeDepth) GRIT_CUDA(cudaEventSynchronize(ev_h2d_[i % kPipeDepth]));
+  return GRIT_OK;
+}
+
+int PackStream::submit(uint64_t i, const void* h_src, uint64_t n_pages, char* err, size_t errlen) {
+  const int b = (int)(i % kPipeDepth);
+  if (n_pages > chunk_pages_ || pages_done_ + n_pages > total_pages_)
+    return fail(err, errlen, GRIT_EINVAL, "chunk %llu out of range", (unsigned long long)i);
+  cudaStream_t s = ctx_->stream;
+  const uint64_t p0 = pages_done_;
+  chunk_page0_[b] = p0;
+  // the H2D may overwrite d_in[b] only after the compaction that last read it
+  if (i >= (uint64_t)kPipeDepth) GRIT_CUDA(cudaStreamWaitEvent(ctx_->h2d, ev_kern_[b], 0));
+  GRIT_CUDA(cudaMemcpyAsync(d_in_[b], h_src, n_pages * kPage, cudaMemcpyHostToDevice, ctx_->h2d));
+  GRIT_CUDA(cudaEventRecord(ev_h2d_[b], ctx_->h2d));
+  h2d_bytes += (double)n_pages * kPage;
+
+  GRIT_CUDA(cudaStreamWaitEvent(s, ev_h2d_[b], 0));
+  // d_out[b] is free once the D2H of its previous chunk is done
+  if (i >= (uint64_t)kPipeDepth) GRIT_CUDA(cudaStreamWaitEvent(s, ev_d2h_[b], 0));
+  if (!timing_started_) {
+    GRIT_CUDA(cudaEventRecord(ctx_->ev0, s));
+    timing_started_ = true;
+  }
+  GRIT_CUDA(launch_analyze(ctx_->geom, ctx_->d_tables, d_in_[b], n_pages, d_crc_ + p0, d_hash_ + p0, d_ref_ + p0, s));
+  GRIT_CUDA(launch_table_insert(ctx_->geom, table_, d_hash_ + p0, d_ref_ + p0, n_pages, kOriginSelf, p0, s));
+  GRIT_CUDA(launch_resolve(ctx_->geom, table_, p0, p0 + n_pages, d_crc_, d_hash_, d_ref_, crcs_, s));
+  const uint64_t tiles = (n_pages + kCompactTile - 1) / kCompactTile;
+  GRIT_CUDA(cudaMemsetAsync(ctx_->d_status, 0, tiles * sizeof(unsigned long long), s));
+  GRIT_CUDA(cudaMemsetAsync(&ctx_->d_cnt->ticket, 0, sizeof(unsigned int), s));
+  GRIT_CUDA(launch_compact(ctx_->geom, d_in_[b], n_pages, d_ref_ + p0, d_out_[b], chunk_pages_, 0, true,
+                           ctx_->d_status, ctx_->d_cnt, s));
+  ctx_->launches += 4;
+  GRIT_CUDA(cudaMemcpyAsync(&h_counts_[b], &ctx_->d_cnt->n_stored, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+  // the next launch continues the slot numbering from here
+  GRIT_CUDA(cudaMemcpyAsync(&ctx_->d_cnt->slot_base, &ctx_->d_cnt->slot_base_next, sizeof(unsigned long long),
+                            cudaMemcpyDeviceToDevice, s));
+  GRIT_CUDA(cudaEventRecord(ev_kern_[b], s));
+  pages_done_ += n_pages;
+  return GRIT_OK;
+}
+
+int PackStream::collect(uint64_t i, void* h_dst, uint64_t* first_slot, uint64_t* n_out, char* err, size_t errlen) {
+  const int b = (int)(i % kPipeDepth);
+  GRIT_CUDA(cudaEventSynchronize(ev_kern_[b]));
+  const uint64_t n = h_counts_[b];
+  *first_slot = slots_done_;
+  *n_out = n;
+  GRIT_CUDA(cudaStreamWaitEvent(ctx_->d2h, ev_kern_[b], 0));
+  if (n) GRIT_CUDA(cudaMemcpyAsync(h_dst, d_out_[b], n * kPage, cudaMemcpyDeviceToHost, ctx_->d2h));
+  GRIT_CUDA(cudaEventRecord(ev_d2h_[b], ctx_->d2h));
+  d2h_bytes += (double)n * kPage;
+  slots_done_ += n;
+  return GRIT_OK;
+}
+
+int PackStream::collect_at(uint64_t i, void* h_dst_base, uint64_t capacity_pages, uint64_t* first_slot,
+                           uint64_t* n_out, char* err, size_t errlen) {
+  const int b = (int)(i % kPipeDepth);
+  GRIT_CUDA(cudaEventSynchronize(ev_kern_[b]));
+  if (slots_done_ + h_counts_[b] > capacity_pages)
+    return fail(err, errlen, GRIT_EINVAL, "packed buffer too small: need more than %llu pages",
+                (unsigned long long)capacity_pages);
+  return collect(i, static_cast<char*>(h_dst_base) + slots_done_ * kPage, first_slot, n_out, err, errlen);
+}
+
+int PackStream::wait_out(uint64_t i, char* err, size_t errlen) {
+  GRIT_CUDA(cudaEventSynchronize(ev_d2h_[i % kPipeDepth]));
+  return GRIT_OK;
+}
+
+int PackStream::finish(uint32_t* h_ref, uint32_t* h_crc, uint64_t* h_hash, grit_pack_stats* stats, char* err,
+                       size_t errlen) {
+  cudaStream_t s = ctx_->stream;
+  if (timing_started_) GRIT_CUDA(cudaEventRecord(ctx_->ev1, s));
+  if (total_pages_) {
+    if (h_ref) GRIT_CUDA(cudaMemcpyAsync(h_ref, d_ref_, total_pages_ * 4, cudaMemcpyDeviceToHost, s));
+    if (h_crc) GRIT_CUDA(cudaMemcpyAsync(h_crc, d_crc_, total_pages_ * 4, cudaMemcpyDeviceToHost, s));
+    if (h_hash) GRIT_CUDA(cudaMemcpyAsync(h_hash, d_hash_, total_pages_ * 8, cudaMemcpyDeviceToHost, s));
+    d2h_bytes += total_pages_ * 16.0;
+  }
+  if (int rc = read_counters(ctx_, s, err, errlen)) return rc;
+  GRIT_CUDA(cudaStreamSynchronize(ctx_->d2h));
+  GRIT_CUDA(cudaStreamSynchronize(ctx_->h2d));
+  if (pages_done_ != total_pages_)
+    return fail(err, errlen, GRIT_EINVAL, "pack stream saw %llu of %llu pages", (unsigned long long)pages_done_,
+                (unsigned long long)total_pages_);
+  const DevCounters& c = *ctx_->h_cnt;
+  if (stats) {
+    stats->n_pages = total_pages_;
+    stats->n_zero = c.kind[0];
+    stats->n_data = c.kind[1];
+    stats->n_dup = c.kind[2];
+    stats->n_parent = c.kind[3];
+    stats->n_peer = c.kind[4];
+    float ms = 0;
+    if (timing_started_) cudaEventElapsedTime(&ms, ctx_->ev0, ctx_->ev1);
+    stats->gpu_ms = ms;
+  }
+  if (c.overflow) return fail(err, errlen, GRIT_EINVAL, "internal: chunk output overflow");
+  return GRIT_OK;
+}
+
+// ------------------------------------------------------------------ restore
+// The packed pages are uploaded once and stay resident (slots are referenced in
+// page order, duplicates point backwards), output chunks are restored and
+// downloaded behind the upload front.
+int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const uint32_t* h_ref,
+                   const uint32_t* h_crc, uint64_t n_pages, const void* parent_image, uint64_t parent_pages,
+                   bool parent_on_device, int verify, uint64_t chunk_pages, grit_restore_stats* stats,
+                   double* h2d_total, double* d2h_total, char* err, size_t errlen) {
+  GRIT_CUDA(cudaSetDevice(ctx->device));
+  if (n_pages > GRIT_MAX_PAGES) return fail(err, errlen, GRIT_EINVAL, "image exceeds GRIT_MAX_PAGES");
+  chunk_pages = std::max<uint64_t>(chunk_pages, 256);
+  const uint64_t n_chunks = (n_pages + chunk_pages - 1) / chunk_pages;
+  const void* h_packed = io.packed_direct;
+  void* h_out = io.out_direct;
+  const bool out_pinned = h_out != nullptr, in_pinned = h_packed != nullptr;
+
+  struct Res {
+    void *d_packed = nullptr, *d_parent = nullptr, *d_out[kPipeDepth] = {}, *h_stage_out[kPipeDepth] = {};
+    bool own_parent = false;
+    void* h_stage_in[2] = {};
+    uint32_t *d_ref = nullptr, *d_crc = nullptr;
+    cudaEvent_t ev_kern[kPipeDepth] = {}, ev_d2h[kPipeDepth] = {};
+    std::vector<cudaEvent_t> ev_up;
+    cudaEvent_t ev_stage[2] = {};
+    ~Res() {
+      cudaDeviceSynchronize();
+      cudaFree(d_packed);
+      if (own_parent) cudaFree(d_parent);
+      cudaFree(d_ref);
+      cudaFree(d_crc);
+      for (int b = 0; b < kPipeDepth; b++) {
+        cudaFree(d_out[b]);
+        if (h_stage_out[b]) cudaFreeHost(h_stage_out[b]);
+        if (ev_kern[b]) cudaEventDestroy(ev_kern[b]);
+        if (ev_d2h[b]) cudaEventDestroy(ev_d2h[b]);
+      }
+      for (int b = 0; b < 2; b++) {
+        if (h_stage_in[b]) cudaFreeHost(h_stage_in[b]);
+        if (ev_stage[b]) cudaEventDestroy(ev_stage[b]);
+      }
+      for (auto e : ev_up) cudaEventDestroy(e);
+    }
+  } r;
+
+  cudaStream_t s = ctx->stream;
+  const size_t chunk_bytes = chunk_pages * kPage;
+  GRIT_CUDA(cudaMalloc(&r.d_packed, std::max<uint64_t>(n_slots, 1) * kPage));
+  GRIT_CUDA(cudaMalloc(&r.d_ref, std::max<uint64_t>(n_pages, 1) * 4));
+  GRIT_CUDA(cudaMalloc(&r.d_crc, std::max<uint64_t>(n_pages, 1) * 4));
+  for (int b = 0; b < kPipeDepth; b++) {
+    GRIT_CUDA(cudaMalloc(&r.d_out[b], chunk_bytes));
+    GRIT_CUDA(cudaEventCreateWithFlags(&r.ev_kern[b], cudaEventDisableTiming));
+    GRIT_CUDA(cudaEventCreateWithFlags(&r.ev_d2h[b], cudaEventDisableTiming));
+    if (!out_pinned) GRIT_CUDA(cudaMallocHost(&r.h_stage_out[b], chunk_bytes));
+  }
+  double h2d = 0, d2h = 0;
+  if (n_pages) {
+    GRIT_CUDA(cudaMemcpyAsync(r.d_ref, h_ref, n_pages * 4, cudaMemcpyHostToDevice, s));
+    if (h_crc) GRIT_CUDA(cudaMemcpyAsync(r.d_crc, h_crc, n_pages * 4, cudaMemcpyHostToDevice, s));
+    h2d += n_pages * 8.0;
+  }
+  PeerImages imgs{};
+  if (parent_image && parent_pages) {
+    if (parent_on_device) {
+      r.d_parent = const_cast<void*>(parent_image);
+    } else {
+      GRIT_CUDA(cudaMalloc(&r.d_parent, parent_pages * kPage));
+      r.own_parent = true;
+      GRIT_CUDA(cudaMemcpyAsync(r.d_parent, parent_image, parent_pages * kPage, cudaMemcpyHostToDevice, s));
+      h2d += (double)parent_pages * kPage;
+    }
+    imgs.parent = static_cast<const unsigned char*>(r.d_parent);
+    imgs.parent_pages = parent_pages;
+  }
+  if (int rc = reset_counters(ctx, s, err, errlen)) return rc;
+
+  // upload the packed pages in chunks on the copy stream, one event per chunk
+  const uint64_t up_chunks = (n_slots + chunk_pages - 1) / chunk_pages;
+  r.ev_up.resize(up_chunks, nullptr);
+  if (!in_pinned && n_slots) {
+    for (int b = 0; b < 2; b++) {
+      GRIT_CUDA(cudaMallocHost(&r.h_stage_in[b], chunk_bytes));
+      GRIT_CUDA(cudaEventCreateWithFlags(&r.ev_stage[b], cudaEventDisableTiming));
+    }
+  }
+  uint64_t uploaded = 0;  // upload chunks enqueued so far
+  auto upload_until = [&](uint64_t slot_end) -> int {
+    const uint64_t need = std::min(up_chunks, (slot_end + chunk_pages - 1) / chunk_pages);
+    for (; uploaded < need; uploaded++) {
+      const uint64_t s0 = uploaded * chunk_pages, n = std::min(chunk_pages, n_slots - s0);
+      const char* src = static_cast<const char*>(h_packed) + s0 * kPage;
+      if (!in_pinned) {  // no pinned source: the caller fills pinned staging
+        const int b = (int)(uploaded & 1);
+        if (uploaded >= 2) GRIT_CUDA(cudaEventSynchronize(r.ev_stage[b]));
+        if (int rc = io.read_packed(s0, n, r.h_stage_in[b])) return fail(err, errlen, rc, "reading packed pages failed");
+        src = static_cast<const char*>(r.h_stage_in[b]);
+      }
+      GRIT_CUDA(cudaMemcpyAsync(static_cast<char*>(r.d_packed) + s0 * kPage, src, n * kPage, cudaMemcpyHostToDevice, ctx->h2d));
+      if (!in_pinned) GRIT_CUDA(cudaEventRecord(r.ev_stage[uploaded & 1], ctx->h2d));
+      GRIT_CUDA(cudaEventCreateWithFlags(&r.ev_up[uploaded], cudaEventDisableTiming));
+      GRIT_CUDA(cudaEventRecord(r.ev_up[uploaded], ctx->h2d));
+      h2d += (double)n * kPage;
+    }
+    return GRIT_OK;
+  };
+
+  GRIT_CUDA(cudaEventRecord(ctx->ev0, s));
+  uint64_t slot_front = 0;  // slots referenced by pages before the current chunk end
+  for (uint64_t i = 0; i < n_chunks + 1; i++) {
+    if (i < n_chunks) {
+      const int b = (int)(i % kPipeDepth);
+      const uint64_t p0 = i * chunk_pages, p1 = std::min(n_pages, p0 + chunk_pages);
+      for (uint64_t p = p0; p < p1; p++)
+        if (GRIT_REF_KIND(h_ref[p]) == GRIT_KIND_DATA) slot_front = std::max<uint64_t>(slot_front, GRIT_REF_VALUE(h_ref[p]) + 1);
+      if (int rc = upload_until(std::min(slot_front, n_slots))) return rc;
+      if (uploaded) GRIT_CUDA(cudaStreamWaitEvent(s, r.ev_up[uploaded - 1], 0));
+      if (i >= (uint64_t)kPipeDepth) GRIT_CUDA(cudaStreamWaitEvent(s, r.ev_d2h[b], 0));
+      GRIT_CUDA(launch_restore(ctx->geom, ctx->d_tables, r.d_packed, n_slots, r.d_ref, r.d_crc, n_pages, p0, p1, imgs,
+                               r.d_out[b], verify, ctx->d_cnt, s));
+      ctx->launches++;
+      GRIT_CUDA(cudaEventRecord(r.ev_kern[b], s));
+      GRIT_CUDA(cudaStreamWaitEvent(ctx->d2h, r.ev_kern[b], 0));
+      char* dst = static_cast<char*>(h_out) + p0 * kPage;
+      if (!out_pinned) {
+        if (i >= (uint64_t)kPipeDepth) {  // staging buffer b still holds chunk i - depth
+          GRIT_CUDA(cudaEventSynchronize(r.ev_d2h[b]));
+          const uint64_t q0 = (i - kPipeDepth) * chunk_pages;
+          if (int rc = io.write_out(q0, q0 + chunk_pages, r.h_stage_out[b])) return fail(err, errlen, rc, "writing restored pages failed");
+        }
+        dst = static_cast<char*>(r.h_stage_out[b]);
+      }
+      GRIT_CUDA(cudaMemcpyAsync(dst, r.d_out[b], (p1 - p0) * kPage, cudaMemcpyDeviceToHost, ctx->d2h));
+      GRIT_CUDA(cudaEventRecord(r.ev_d2h[b], ctx->d2h));
+      d2h += (double)(p1 - p0) * kPage;
+    }
+  }
+  if (int rc = upload_until(n_slots)) return rc;  // nothing may be left half-sent
+  GRIT_CUDA(cudaEventRecord(ctx->ev1, s));
+  if (int rc = read_counters(ctx, s, err, errlen)) return rc;
+  GRIT_CUDA(cudaStreamSynchronize(ctx->d2h));
+  GRIT_CUDA(cudaStreamSynchronize(ctx->h2d));
+  if (!out_pinned) {  // drain the staged tail
+    const uint64_t first = n_chunks > (uint64_t)kPipeDepth ? n_chunks - kPipeDepth : 0;
+    for (uint64_t i = first; i < n_chunks; i++) {
+      const uint64_t p0 = i * chunk_pages, p1 = std::min(n_pages, p0 + chunk_pages);
+      if (int rc = io.write_out(p0, p1, r.h_stage_out[i % kPipeDepth])) return fail(err, errlen, rc, "writing restored pages failed");
+    }
+  }
+  if (h2d_total) *h2d_total += h2d;
+  if (d2h_total) *d2h_total += d2h;
+  const DevCounters& c = *ctx->h_cnt;
+  if (stats) {
+    stats->n_pages = n_pages;
+    stats->n_bad = c.n_bad;
+    stats->first_bad = c.first_bad;
+    float ms = 0;
+    cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+    stats->gpu_ms = ms;
+  }
+  if (c.n_bad)
+    return fail(err, errlen, GRIT_ECRC, "restore: %llu page(s) failed CRC-32C or had a bad reference, first page %llu",
+                (unsigned long long)c.n_bad, (unsigned long long)c.first_bad);
+  return GRIT_OK;
+}
+
+}  // namespace grit
+
+extern "C" {
+
+int grit_pin_host(void* h_ptr, size_t bytes) {
+  return cudaHostRegister(h_ptr, bytes, cudaHostRegisterDefault) == cudaSuccess ? GRIT_OK : GRIT_ECUDA;
+}
+int grit_unpin_host(void* h_ptr) { return cudaHostUnregister(h_ptr) == cudaSuccess ? GRIT_OK : GRIT_ECUDA; }
+
+int grit_pack_host(grit_ctx* ctx, const void* h_image, uint64_t n_pages, const grit_table* parent, void* h_packed,
+                   uint64_t capacity_pages, uint32_t* h_ref, uint32_t* h_crc, uint64_t* h_hash, grit_pack_stats* stats,
+                   char* err, size_t errlen) {
+  if (!ctx) return fail(err, errlen, GRIT_EINVAL, "null context");
+  if (n_pages && (!h_image || !h_ref || !h_crc || !h_hash || (!h_packed && capacity_pages)))
+    return fail(err, errlen, GRIT_EINVAL, "null buffer");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  GRIT_CUDA(cudaSetDevice(ctx->device));
+  const uint64_t chunk_pages = (64ull << 20) / kPage;
+  const uint64_t n_chunks = (n_pages + chunk_pages - 1) / chunk_pages;
+  const bool in_pinned = is_pinned(h_image), out_pinned = is_pinned(h_packed);
+  PackStream ps(ctx, n_pages, chunk_pages);
+  if (int rc = ps.begin(parent, err, errlen)) return rc;
+  // pageable caller memory is bounced through pinned staging (one memcpy each way)
+  if (n_pages)
+    if (int rc = ps.alloc_staging(!in_pinned, !out_pinned, err, errlen)) return rc;
+  struct Pending {
+    uint64_t first_slot, n_out;
+  } pend[kPipeDepth] = {};
+  auto drain = [&](uint64_t i) -> int {  // chunk i's D2H -> caller memory (staged mode only)
+    if (int rc = ps.wait_out(i, err, errlen)) return rc;
+    if (!out_pinned) {
+      const Pending& p = pend[i % kPipeDepth];
+      memcpy(static_cast<char*>(h_packed) + p.first_slot * kPage, ps.out_buffer(i), p.n_out * kPage);
+    }
+    return GRIT_OK;
+  };
+  for (uint64_t i = 0; i <= n_chunks; i++) {
+    if (i < n_chunks) {
+      const uint64_t p0 = i * chunk_pages, n = std::min(chunk_pages, n_pages - p0);
+      const void* src = static_cast<const char*>(h_image) + p0 * kPage;
+      if (!in_pinned) {
+        if (int rc = ps.wait_in_free(i, err, errlen)) return rc;
+        memcpy(ps.in_buffer(i), src, n * kPage);
+        src = ps.in_buffer(i);
+      }
+      if (i >= (uint64_t)kPipeDepth && !out_pinned)  // staging out buffer about to be reused
+        if (int rc = drain(i - kPipeDepth)) return rc;
+      if (int rc = ps.submit(i, src, n, err, errlen)) return rc;
+    }
+    if (i >= 1) {
+      const uint64_t j = i - 1;
+      Pending& p = pend[j % kPipeDepth];
+      int rc;
+      if (out_pinned) {
+        rc = ps.collect_at(j, h_packed, capacity_pages, &p.first_slot, &p.n_out, err, errlen);
+      } else {
+        rc = ps.collect(j, ps.out_buffer(j), &p.first_slot, &p.n_out, err, errlen);
+        if (!rc && p.first_slot + p.n_out > capacity_pages)
+          rc = fail(err, errlen, GRIT_EINVAL, "packed buffer too small: need more than %llu pages",
+                    (unsigned long long)capacity_pages);
+      }
+      if (rc) return rc;
+    }
+  }
+  if (!out_pinned) {
+    const uint64_t first = n_chunks > (uint64_t)kPipeDepth ? n_chunks - kPipeDepth : 0;
+    for (uint64_t i = first; i < n_chunks; i++)
+      if (int rc = drain(i)) return rc;
+  }
+  return ps.finish(h_ref, h_crc, h_hash, stats, err, errlen);
+}
+
+int grit_restore_host(grit_ctx* ctx, const void* h_packed, uint64_t n_slots, const uint32_t* h_ref,
+                      const uint32_t* h_crc, uint64_t n_pages, const void* h_parent_image, uint64_t parent_pages,
+                      void* h_out, int verify, grit_restore_stats* stats, char* err, size_t errlen) {
+  if (!ctx) return fail(err, errlen, GRIT_EINVAL, "null context");
+  if (n_pages && (!h_ref || !h_out || (verify && !h_crc) || (n_slots && !h_packed)))
+    return fail(err, errlen, GRIT_EINVAL, "null buffer");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  RestoreIO io;
+  if (is_pinned(h_packed)) {
+    io.packed_direct = h_packed;
+  } else {
+    io.read_packed = [&](uint64_t s0, uint64_t n, void* dst) {
+      memcpy(dst, static_cast<const char*>(h_packed) + s0 * kPage, n * kPage);
+      return 0;
+    };
+  }
+  if (is_pinned(h_out)) {
+    io.out_direct = h_out;
+  } else {
+    io.write_out = [&](uint64_t p0, uint64_t p1, const void* src) {
+      memcpy(static_cast<char*>(h_out) + p0 * kPage, src, (p1 - p0) * kPage);
+      return 0;
+    };
+  }
+  return restore_stream(ctx, io, n_slots, h_ref, h_crc, n_pages, h_parent_image, parent_pages, false, verify,
+                        (64ull << 20) / kPage, stats, nullptr, nullptr, err, errlen);
+}
+
+}  // extern "C"

@@ -1,0 +1,580 @@
+// Page kernels of gritpack for sm_100a (B200).  HBM-bound byte/integer work:
+// 128-bit coalesced loads, one persistent CTA per SM for the CRC kernels (the
+// lane-private GF(2) tables fill most of the SM's shared memory), grids sized in
+// multiples of the SM count for the rest.  No tensor-core path: nothing here is
+// GEMM shaped.
+//
+// None of this has a counterpart under /root/reference: the reference's data
+// mover is io.Copy (pkg/gritagent/copy/copy.go:79).  BASELINE.json north_star
+// defines the work; gf2_tables.h explains the CRC algebra.
+#include "kernels.h"
+
+namespace grit {
+
+extern __shared__ __align__(1024) unsigned char smem[];
+
+namespace {
+
+constexpr int kWarps = 16;
+constexpr int kThreads = kWarps * 32;
+
+// shared memory map of the CRC kernels (bytes)
+constexpr uint32_t kSmA = 0;             // A tables, one copy per lane: 128 KiB
+constexpr uint32_t kSmT = 128 * 1024;    // T tables, shared: 4 KiB
+constexpr uint32_t kSmW = kSmT + 4096;   // W[l] tables, shared: 32 KiB
+constexpr uint32_t kSmBytes = kSmW + 32768;
+
+constexpr unsigned long long kGold = 0x9E3779B97F4A7C15ull;
+constexpr unsigned long long kFmul = 0xD6E8FEB86659FD93ull;
+
+__host__ __device__ constexpr unsigned long long sm64(unsigned long long x) {
+  x += 0x9E3779B97F4A7C15ull;
+  unsigned long long z = x;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  return z ^ (z >> 31);
+}
+
+// NH keys: K[n] = hi32(sm64^(n+1)("gritpak1")) | 1, n = 4*jj + i
+__host__ __device__ constexpr uint32_t nh_key(int n) {
+  unsigned long long s = 0x6772697470616B31ull;
+  for (int k = 0; k <= n; k++) s = sm64(s);
+  return (uint32_t)(s >> 32) | 1u;
+}
+template <int N>
+struct NhKey {
+  static constexpr uint32_t v = nh_key(N);
+};
+
+__device__ __forceinline__ unsigned long long fmix(unsigned long long x) {
+  x ^= x >> 32;
+  x *= kFmul;
+  x ^= x >> 32;
+  x *= kFmul;
+  x ^= x >> 32;
+  return x;
+}
+
+__device__ __forceinline__ uint4 ldg_stream(const uint4* p) {
+  uint4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(p));
+  return v;
+}
+__device__ __forceinline__ void stg_stream(uint4* p, const uint4& v) {
+  asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y),
+               "r"(v.z), "r"(v.w)
+               : "memory");
+}
+
+__device__ __forceinline__ uint32_t lds32(uint32_t byte_off) {
+  return *reinterpret_cast<const uint32_t*>(smem + byte_off);
+}
+
+// Expand the GF(2) tables into shared memory.  A[k][e] gets one copy per lane so
+// that bank == lane for every lookup: entry e of tables 2r and 2r+1 live in the
+// 256-byte row e of 64 KiB region r, table 2r in the first 128 bytes.
+__device__ __forceinline__ void load_tables(const Gf2Tables* __restrict__ g) {
+  uint32_t* s = reinterpret_cast<uint32_t*>(smem);
+  for (uint32_t idx = threadIdx.x; idx < 4u * 256u * 32u; idx += blockDim.x) {
+    uint32_t lane = idx & 31, e = (idx >> 5) & 255, k = idx >> 13;
+    s[(k >> 1) * 16384 + e * 64 + (k & 1) * 32 + lane] = g->A[k][e];
+  }
+  const uint32_t* t = &g->T[0][0];
+  for (uint32_t idx = threadIdx.x; idx < 1024; idx += blockDim.x) s[kSmT / 4 + idx] = t[idx];
+  const uint32_t* w = &g->W[0][0][0];
+  for (uint32_t idx = threadIdx.x; idx < 8192; idx += blockDim.x) s[kSmW / 4 + idx] = w[idx];
+  __syncthreads();
+}
+
+// adv(128, c): one PRMT builds (byte << 8) | lane*4, the table select is the
+// LDS immediate, so a lookup costs one ALU op and one conflict-free LDS.
+__device__ __forceinline__ uint32_t adv128(uint32_t c, uint32_t lane4) {
+  uint32_t a0 = __byte_perm(c, lane4, 0x5504);
+  uint32_t a1 = __byte_perm(c, lane4, 0x5514);
+  uint32_t a2 = __byte_perm(c, lane4, 0x5524);
+  uint32_t a3 = __byte_perm(c, lane4, 0x5534);
+  return lds32(kSmA + a0) ^ lds32(kSmA + 128 + a1) ^ lds32(kSmA + 65536 + a2) ^
+         lds32(kSmA + 65536 + 128 + a3);
+}
+
+__device__ __forceinline__ uint32_t adv_shared(uint32_t d, uint32_t base) {
+  return lds32(base + ((d & 0xFF) << 2)) ^ lds32(base + 1024 + ((d >> 6) & 0x3FC)) ^
+         lds32(base + 2048 + ((d >> 14) & 0x3FC)) ^ lds32(base + 3072 + ((d >> 22) & 0x3FC));
+}
+
+// Per-lane running state over one page: four CRC chains (one per word slot of
+// the lane's 16-byte segments), the OR of all words, the NH accumulator.
+struct PageAcc {
+  uint32_t c0, c1, c2, c3;
+  uint32_t z;
+  unsigned long long h;
+};
+
+template <int JJ, bool kFirst, bool kHash>
+__device__ __forceinline__ void absorb(PageAcc& a, const uint4& v, uint32_t lane4) {
+  if (kFirst) {
+    a.c0 = v.x;
+    a.c1 = v.y;
+    a.c2 = v.z;
+    a.c3 = v.w;
+  } else {
+    a.c0 = adv128(a.c0, lane4) ^ v.x;
+    a.c1 = adv128(a.c1, lane4) ^ v.y;
+    a.c2 = adv128(a.c2, lane4) ^ v.z;
+    a.c3 = adv128(a.c3, lane4) ^ v.w;
+  }
+  if (kHash) {
+    a.z |= v.x | v.y | v.z | v.w;
+    a.h += (unsigned long long)(v.x + NhKey<4 * JJ + 0>::v) * (unsigned long long)(v.y + NhKey<4 * JJ + 1>::v);
+    a.h += (unsigned long long)(v.z + NhKey<4 * JJ + 2>::v) * (unsigned long long)(v.w + NhKey<4 * JJ + 3>::v);
+  }
+}
+
+template <bool kFirstBatch, bool kHash>
+__device__ __forceinline__ void absorb_batch(PageAcc& a, const uint4 (&v)[8], uint32_t lane4) {
+  if (kHash && !kFirstBatch) a.h *= kGold;
+  absorb<0, kFirstBatch, kHash>(a, v[0], lane4);
+  absorb<1, false, kHash>(a, v[1], lane4);
+  absorb<2, false, kHash>(a, v[2], lane4);
+  absorb<3, false, kHash>(a, v[3], lane4);
+  absorb<4, false, kHash>(a, v[4], lane4);
+  absorb<5, false, kHash>(a, v[5], lane4);
+  absorb<6, false, kHash>(a, v[6], lane4);
+  absorb<7, false, kHash>(a, v[7], lane4);
+}
+
+// Fold the lane's four chains, weight by the lane's position, XOR over the
+// 8-lane group: the CRC-32C of the page (valid in every lane of the group).
+__device__ __forceinline__ uint32_t finish_crc(const PageAcc& a, uint32_t l) {
+  uint32_t d = a.c0;
+  d = adv_shared(d, kSmT) ^ a.c1;
+  d = adv_shared(d, kSmT) ^ a.c2;
+  d = adv_shared(d, kSmT) ^ a.c3;
+  uint32_t r = adv_shared(d, kSmW + l * 4096);
+  r ^= __shfl_xor_sync(0xFFFFFFFFu, r, 1);
+  r ^= __shfl_xor_sync(0xFFFFFFFFu, r, 2);
+  r ^= __shfl_xor_sync(0xFFFFFFFFu, r, 4);
+  return r ^ kCrcZeroPage;
+}
+
+__device__ __forceinline__ unsigned long long finish_hash(const PageAcc& a, uint32_t l) {
+  unsigned long long v = fmix(a.h + (unsigned long long)(l + 1) * kFmul);
+  v += __shfl_xor_sync(0xFFFFFFFFu, v, 1);
+  v += __shfl_xor_sync(0xFFFFFFFFu, v, 2);
+  v += __shfl_xor_sync(0xFFFFFFFFu, v, 4);
+  v = fmix(v ^ kGold);
+  return v ? v : 1ull;
+}
+
+__device__ __forceinline__ void load_batch(uint4 (&v)[8], const uint4* src, bool on) {
+#pragma unroll
+  for (int j = 0; j < 8; j++) v[j] = on ? ldg_stream(src + 8 * j) : make_uint4(0, 0, 0, 0);
+}
+
+// ------------------------------------------------------------------ K1 analyze
+// A warp takes four consecutive pages per step; lanes 8g..8g+7 own page g.
+__global__ void __launch_bounds__(kThreads, 1)
+k_analyze(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ image, uint64_t n_pages,
+          uint32_t* __restrict__ crc, unsigned long long* __restrict__ hash, uint32_t* __restrict__ ref) {
+  load_tables(tabs);
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t g = lane >> 3, l = lane & 7, lane4 = lane * 4;
+  const uint64_t n_groups = (n_pages + 3) / 4;
+  const uint64_t stride = (uint64_t)gridDim.x * kWarps;
+  uint64_t grp = (uint64_t)blockIdx.x * kWarps + warp;
+  if (grp >= n_groups) return;
+
+  uint4 cur[8], nxt[8];
+  uint64_t p = 4 * grp + g;
+  const uint4* src = image + p * 256 + l;
+  load_batch(cur, src, p < n_pages);
+  for (; grp < n_groups; grp += stride) {
+    PageAcc a;
+    a.z = 0;
+    a.h = 0;
+    const bool on = p < n_pages;
+    load_batch(nxt, src + 64, on);
+    absorb_batch<true, true>(a, cur, lane4);
+    load_batch(cur, src + 128, on);
+    absorb_batch<false, true>(a, nxt, lane4);
+    load_batch(nxt, src + 192, on);
+    absorb_batch<false, true>(a, cur, lane4);
+    // prefetch the first batch of this warp's next group
+    const uint64_t p_next = 4 * (grp + stride) + g;
+    const uint4* src_next = image + p_next * 256 + l;
+    load_batch(cur, src_next, (grp + stride < n_groups) && p_next < n_pages);
+    absorb_batch<false, true>(a, nxt, lane4);
+
+    const uint32_t page_crc = finish_crc(a, l);
+    uint32_t z = a.z;
+    z |= __shfl_xor_sync(0xFFFFFFFFu, z, 1);
+    z |= __shfl_xor_sync(0xFFFFFFFFu, z, 2);
+    z |= __shfl_xor_sync(0xFFFFFFFFu, z, 4);
+    const unsigned long long page_hash = finish_hash(a, l);
+    if (l == 0 && on) {
+      crc[p] = page_crc;
+      hash[p] = page_hash;
+      ref[p] = z ? kRefPending : 0u;
+    }
+    p = p_next;
+    src = src_next;
+  }
+}
+
+// ------------------------------------------------------------------ K2 dedup
+__device__ __forceinline__ uint64_t table_home(unsigned long long h, uint64_t mask) {
+  return ((h * kGold) >> 20) & mask;
+}
+
+__global__ void __launch_bounds__(256)
+k_table_insert(DedupTable t, const unsigned long long* __restrict__ hash, const uint32_t* __restrict__ ref,
+               uint64_t n, uint32_t origin, uint64_t index_base) {
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (uint64_t)gridDim.x * blockDim.x) {
+    if (ref && ref[i] == 0u) continue;  // zero pages never enter the table
+    const unsigned long long h = hash[i];
+    const uint32_t v = origin << 26 | (uint32_t)(index_base + i);
+    for (uint64_t s = table_home(h, t.mask);; s = (s + 1) & t.mask) {
+      unsigned long long k = t.keys[s];
+      if (k == 0ull) k = atomicCAS(&t.keys[s], 0ull, h);
+      if (k == 0ull || k == h) {
+        atomicMin(&t.vals[s], v);
+        break;
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256)
+k_resolve(DedupTable t, uint64_t page0, uint64_t page1, const uint32_t* __restrict__ crc,
+          const unsigned long long* __restrict__ hash, uint32_t* __restrict__ ref, PeerCrcs crcs) {
+  for (uint64_t p = page0 + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; p < page1;
+       p += (uint64_t)gridDim.x * blockDim.x) {
+    if (ref[p] == 0u) continue;
+    const unsigned long long h = hash[p];
+    uint64_t s = table_home(h, t.mask);
+    while (t.keys[s] != h) s = (s + 1) & t.mask;  // inserted by k_table_insert
+    const uint32_t v = t.vals[s], origin = v >> 26, idx = v & ((1u << 26) - 1);
+    uint32_t out = kRefKeep;
+    if (!(origin == kOriginSelf && idx == (uint32_t)p)) {
+      const uint32_t ocrc = origin == 0             ? crcs.parent[idx]
+                            : origin == kOriginSelf ? crc[idx]
+                                                    : crcs.peer[origin - 1][idx];
+      if (ocrc == crc[p]) {
+        out = origin == 0             ? (3u << 29 | idx)
+              : origin == kOriginSelf ? (2u << 29 | idx)
+                                      : (4u << 29 | (origin - 1) << 26 | idx);
+      }
+    }
+    ref[p] = out;
+  }
+}
+
+// ------------------------------------------------------------------ K3 compact
+// Single pass: per 256-page tile, ballot-count the pages to keep, get the tile's
+// exclusive prefix by decoupled look-back over the tile status words, assign
+// slots in page order, then all warps copy the kept pages with 128-bit accesses.
+constexpr unsigned long long kFlagAgg = 1ull << 62, kFlagIncl = 2ull << 62;
+
+__device__ __forceinline__ unsigned long long ld_status(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_status(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+__global__ void __launch_bounds__(256)
+k_compact(const uint4* __restrict__ image, uint64_t n_pages, uint32_t* __restrict__ ref,
+          uint4* __restrict__ packed, uint64_t capacity_pages, uint64_t slot_base, int chained,
+          unsigned long long* __restrict__ status, DevCounters* __restrict__ cnt) {
+  __shared__ uint32_t s_tile, s_warp_cnt[8], s_excl;
+  __shared__ uint16_t s_list[kCompactTile];
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t n_tiles = (uint32_t)((n_pages + kCompactTile - 1) / kCompactTile);
+  // chained (streaming) mode: slots continue from the previous launch's total, which only
+  // the device knows; the packed buffer then holds just this launch's pages, from index 0.
+  const uint64_t ref_base = chained ? cnt->slot_base : slot_base;
+  const uint64_t out_base = chained ? 0 : slot_base;
+
+  for (;;) {
+    if (threadIdx.x == 0) s_tile = atomicAdd(&cnt->ticket, 1u);
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    if (tile >= n_tiles) return;
+    const uint64_t p = (uint64_t)tile * kCompactTile + threadIdx.x;
+    const uint32_t r = p < n_pages ? ref[p] : 0u;
+    const bool keep = r == kRefKeep;
+
+    const uint32_t bal = __ballot_sync(0xFFFFFFFFu, keep);
+    if (lane == 0) s_warp_cnt[warp] = __popc(bal);
+    // per-kind page counts for the stats (a few smem-free block reductions)
+    const uint32_t kind = keep ? 1u : (p < n_pages ? r >> 29 : 7u);
+    const int n_zero = __syncthreads_count(kind == 0u);
+    const int n_dup = __syncthreads_count(kind == 2u);
+    const int n_par = __syncthreads_count(kind == 3u);
+    const int n_peer = __syncthreads_count(kind == 4u);
+
+    uint32_t before = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < 8; w++) {
+      const uint32_t c = s_warp_cnt[w];
+      before += w < (int)warp ? c : 0u;
+      total += c;
+    }
+    if (threadIdx.x == 0) {
+      if (n_zero) atomicAdd(&cnt->kind[0], (unsigned long long)n_zero);
+      if (total) atomicAdd(&cnt->kind[1], (unsigned long long)total);
+      if (n_dup) atomicAdd(&cnt->kind[2], (unsigned long long)n_dup);
+      if (n_par) atomicAdd(&cnt->kind[3], (unsigned long long)n_par);
+      if (n_peer) atomicAdd(&cnt->kind[4], (unsigned long long)n_peer);
+    }
+
+    if (warp == 0) {
+      if (lane == 0) st_status(&status[tile], (tile == 0 ? kFlagIncl : kFlagAgg) | total);
+      uint32_t excl = 0;
+      if (tile > 0) {
+        int64_t look = (int64_t)tile - 1;
+        for (;;) {
+          const int64_t idx = look - lane;
+          unsigned long long st;
+          do {
+            st = idx >= 0 ? ld_status(&status[idx]) : kFlagIncl;
+          } while (__any_sync(0xFFFFFFFFu, (st >> 62) == 0));
+          const uint32_t incl = __ballot_sync(0xFFFFFFFFu, (st >> 62) == 2);
+          const uint32_t upto = incl ? (uint32_t)__ffs(incl) - 1u : 31u;
+          uint32_t v = lane <= upto ? (uint32_t)st : 0u;
+#pragma unroll
+          for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
+          excl += v;
+          if (incl) break;
+          look -= 32;
+        }
+        if (lane == 0) st_status(&status[tile], kFlagIncl | (excl + total));
+      }
+      if (lane == 0) {
+        s_excl = excl;
+        if (tile == n_tiles - 1) {
+          cnt->n_stored = excl + total;
+          cnt->slot_base_next = ref_base + excl + total;
+        }
+      }
+    }
+    const uint32_t rank = before + __popc(bal & ((1u << lane) - 1));
+    if (keep) s_list[rank] = (uint16_t)threadIdx.x;
+    __syncthreads();
+    const uint64_t first_slot = out_base + s_excl;
+    if (keep) {
+      ref[p] = 1u << 29 | (uint32_t)(ref_base + s_excl + rank);
+      if (first_slot + rank >= capacity_pages) atomicAdd(&cnt->overflow, 1ull);
+    }
+    // copy: one page per warp per step, two steps in flight
+    for (uint32_t k = warp; k < total; k += 16) {
+      const uint32_t k2 = k + 8;
+      const bool two = k2 < total;
+      const uint64_t sa = first_slot + k, sb = first_slot + k2;
+      const uint4* a = image + ((uint64_t)tile * kCompactTile + s_list[k]) * 256 + lane;
+      const uint4* b = image + ((uint64_t)tile * kCompactTile + s_list[two ? k2 : k]) * 256 + lane;
+      uint4 va[8], vb[8];
+#pragma unroll
+      for (int j = 0; j < 8; j++) va[j] = ldg_stream(a + 32 * j);
+      if (two) {
+#pragma unroll
+        for (int j = 0; j < 8; j++) vb[j] = ldg_stream(b + 32 * j);
+      }
+      if (sa < capacity_pages) {
+#pragma unroll
+        for (int j = 0; j < 8; j++) stg_stream(packed + sa * 256 + lane + 32 * j, va[j]);
+      }
+      if (two && sb < capacity_pages) {
+#pragma unroll
+        for (int j = 0; j < 8; j++) stg_stream(packed + sb * 256 + lane + 32 * j, vb[j]);
+      }
+    }
+    __syncthreads();  // s_tile, s_list reused by the next tile
+  }
+}
+
+// ------------------------------------------------------------------ K4 restore
+__global__ void __launch_bounds__(kThreads, 1)
+k_restore(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ packed, uint64_t n_slots,
+          const uint32_t* __restrict__ ref, const uint32_t* __restrict__ crc, uint64_t n_pages,
+          uint64_t page0, uint64_t page1, PeerImages imgs, uint4* __restrict__ out, int verify,
+          DevCounters* __restrict__ cnt) {
+  if (verify) load_tables(tabs);
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t g = lane >> 3, l = lane & 7, lane4 = lane * 4;
+  const uint64_t n_groups = (page1 - page0 + 3) / 4;
+  const uint64_t stride = (uint64_t)gridDim.x * kWarps;
+
+  // restores pages [page0, page1) of the image into out[0 .. page1-page0)
+  for (uint64_t grp = (uint64_t)blockIdx.x * kWarps + warp; grp < n_groups; grp += stride) {
+    const uint64_t p = page0 + 4 * grp + g;
+    const bool on = p < page1;
+    // follow the page reference to the 4 KiB that holds its bytes
+    const uint4* src = nullptr;
+    bool bad = false;
+    if (on) {
+      uint32_t r = ref[p], kind = r >> 29, v = r & 0x1FFFFFFFu;
+      if (kind == 2u) {  // DUP -> the owner's slot
+        const uint32_t r2 = v < n_pages ? ref[v] : 0u;
+        bad = (r2 >> 29) != 1u;
+        kind = 1u;
+        v = r2 & 0x1FFFFFFFu;
+      }
+      if (kind == 1u) {
+        if (!bad && v < n_slots) src = packed + (uint64_t)v * 256;
+        else bad = true;
+      } else if (kind == 3u) {
+        if (imgs.parent && v < imgs.parent_pages) src = reinterpret_cast<const uint4*>(imgs.parent) + (uint64_t)v * 256;
+        else bad = true;
+      } else if (kind == 4u) {
+        const uint32_t rk = v >> 26, idx = v & ((1u << 26) - 1);
+        if (rk < imgs.n_peers && imgs.peer[rk] && idx < imgs.peer_pages[rk])
+          src = reinterpret_cast<const uint4*>(imgs.peer[rk]) + (uint64_t)idx * 256;
+        else bad = true;
+      } else if (kind != 0u) {
+        bad = true;
+      }
+    }
+    const bool have = src != nullptr;
+    const uint4* s = have ? src + l : packed;  // never dereferenced when !have
+    uint4* d = out + (p - page0) * 256 + l;
+    PageAcc a;
+    a.z = 0;
+    a.h = 0;
+    uint4 cur[8], nxt[8];
+    load_batch(cur, s, have);
+    load_batch(nxt, s + 64, have);
+    if (on) {
+#pragma unroll
+      for (int j = 0; j < 8; j++) stg_stream(d + 8 * j, cur[j]);
+    }
+    if (verify) absorb_batch<true, false>(a, cur, lane4);
+    load_batch(cur, s + 128, have);
+    if (on) {
+#pragma unroll
+      for (int j = 0; j < 8; j++) stg_stream(d + 64 + 8 * j, nxt[j]);
+    }
+    if (verify) absorb_batch<false, false>(a, nxt, lane4);
+    load_batch(nxt, s + 192, have);
+    if (on) {
+#pragma unroll
+      for (int j = 0; j < 8; j++) stg_stream(d + 128 + 8 * j, cur[j]);
+    }
+    if (verify) absorb_batch<false, false>(a, cur, lane4);
+    if (on) {
+#pragma unroll
+      for (int j = 0; j < 8; j++) stg_stream(d + 192 + 8 * j, nxt[j]);
+    }
+    if (verify) {
+      absorb_batch<false, false>(a, nxt, lane4);
+      const uint32_t page_crc = finish_crc(a, l);
+      if (have && page_crc != crc[p]) bad = true;
+    }
+    if (bad && l == 0) {
+      atomicAdd(&cnt->n_bad, 1ull);
+      atomicMin(&cnt->first_bad, (unsigned long long)p);
+    }
+  }
+}
+
+// ------------------------------------------------------------------ K5 synth
+__global__ void __launch_bounds__(256)
+k_synth(uint4* __restrict__ image, uint64_t n_pages, uint64_t page_base, unsigned long long seed,
+        uint32_t pct_zero, uint32_t pct_dup, uint32_t dup_pool) {
+  const uint64_t n = n_pages * 256;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (uint64_t)gridDim.x * blockDim.x) {
+    const uint64_t gp = page_base + (i >> 8);
+    const uint32_t seg = (uint32_t)i & 255;
+    const unsigned long long r = sm64(seed ^ (gp * kGold));
+    const uint32_t cls = (uint32_t)(r % 100);
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (cls >= pct_zero) {
+      unsigned long long key = gp;
+      if (cls < pct_zero + pct_dup && dup_pool) key = 1ull << 63 | ((r >> 32) % dup_pool);
+      const unsigned long long base = sm64(seed ^ sm64(key));
+      const unsigned long long lo = sm64(base + 2ull * seg), hi = sm64(base + 2ull * seg + 1);
+      v = make_uint4((uint32_t)lo, (uint32_t)(lo >> 32), (uint32_t)hi, (uint32_t)(hi >> 32));
+    }
+    image[i] = v;
+  }
+}
+
+int grid_for(const LaunchGeom& g, uint64_t n_items, int per_block, int blocks_per_sm) {
+  const uint64_t need = (n_items + per_block - 1) / per_block;
+  const uint64_t cap = (uint64_t)g.sm_count * blocks_per_sm;
+  return (int)(need < cap ? (need ? need : 1) : cap);
+}
+
+}  // namespace
+
+uint32_t page_kernel_smem_bytes() { return kSmBytes; }
+
+cudaError_t configure_kernels() {
+  cudaError_t e = cudaFuncSetAttribute(k_analyze, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmBytes);
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(k_restore, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmBytes);
+}
+
+cudaError_t launch_analyze(const LaunchGeom& g, const Gf2Tables* d_tab, const void* d_image, uint64_t n_pages,
+                           uint32_t* d_crc, uint64_t* d_hash, uint32_t* d_ref, cudaStream_t s) {
+  if (!n_pages) return cudaSuccess;
+  const int grid = grid_for(g, (n_pages + 3) / 4, kWarps, 1);
+  k_analyze<<<grid, kThreads, kSmBytes, s>>>(d_tab, static_cast<const uint4*>(d_image), n_pages, d_crc,
+                                             reinterpret_cast<unsigned long long*>(d_hash), d_ref);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_table_insert(const LaunchGeom& g, DedupTable t, const uint64_t* d_hash,
+                                const uint32_t* d_ref_or_null, uint64_t n, uint32_t origin, uint64_t index_base,
+                                cudaStream_t s) {
+  if (!n) return cudaSuccess;
+  k_table_insert<<<grid_for(g, n, 256, 8), 256, 0, s>>>(
+      t, reinterpret_cast<const unsigned long long*>(d_hash), d_ref_or_null, n, origin, index_base);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_resolve(const LaunchGeom& g, DedupTable t, uint64_t page0, uint64_t page1, const uint32_t* d_crc,
+                           const uint64_t* d_hash, uint32_t* d_ref, PeerCrcs crcs, cudaStream_t s) {
+  if (page1 <= page0) return cudaSuccess;
+  k_resolve<<<grid_for(g, page1 - page0, 256, 8), 256, 0, s>>>(
+      t, page0, page1, d_crc, reinterpret_cast<const unsigned long long*>(d_hash), d_ref, crcs);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_compact(const LaunchGeom& g, const void* d_image, uint64_t n_pages, uint32_t* d_ref,
+                           void* d_packed, uint64_t capacity_pages, uint64_t slot_base, bool chained,
+                           unsigned long long* d_tile_status, DevCounters* d_cnt, cudaStream_t s) {
+  if (!n_pages) return cudaSuccess;
+  k_compact<<<grid_for(g, n_pages, kCompactTile, 8), 256, 0, s>>>(
+      static_cast<const uint4*>(d_image), n_pages, d_ref, static_cast<uint4*>(d_packed), capacity_pages,
+      slot_base, chained ? 1 : 0, d_tile_status, d_cnt);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_restore(const LaunchGeom& g, const Gf2Tables* d_tab, const void* d_packed, uint64_t n_slots,
+                           const uint32_t* d_ref, const uint32_t* d_crc, uint64_t n_pages, uint64_t page0,
+                           uint64_t page1, PeerImages imgs, void* d_out, int verify, DevCounters* d_cnt,
+                           cudaStream_t s) {
+  if (page1 <= page0) return cudaSuccess;
+  const int grid = grid_for(g, (page1 - page0 + 3) / 4, kWarps, 1);
+  k_restore<<<grid, kThreads, verify ? kSmBytes : 0, s>>>(d_tab, static_cast<const uint4*>(d_packed), n_slots,
+                                                          d_ref, d_crc, n_pages, page0, page1, imgs,
+                                                          static_cast<uint4*>(d_out), verify, d_cnt);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_synth(const LaunchGeom& g, void* d_image, uint64_t n_pages, uint64_t page_base, uint64_t seed,
+                         uint32_t pct_zero, uint32_t pct_dup, uint32_t dup_pool, cudaStream_t s) {
+  if (!n_pages) return cudaSuccess;
+  k_synth<<<grid_for(g, n_pages * 256, 256, 8), 256, 0, s>>>(static_cast<uint4*>(d_image), n_pages, page_base,
+                                                             seed, pct_zero, pct_dup, dup_pool);
+  return cudaGetLastError();
+}
+
+}  // namespace grit

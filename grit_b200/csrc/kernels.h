@@ -1,0 +1,77 @@
+// Launchers of the sm_100a page kernels (kernels.cu).  Internal to libgritpack;
+// the C ABI in api.cu / hostpipe.cu / dirpack.cpp is the public surface.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "gf2_tables.h"
+
+namespace grit {
+
+constexpr uint32_t kPage = 4096;
+constexpr uint32_t kRefPending = 0xFFFFFFFFu;  // K1: non-zero page, not yet resolved
+constexpr uint32_t kRefKeep = 0xFFFFFFFEu;     // K2: must be stored, slot not yet assigned
+constexpr uint32_t kOriginSelf = 15;
+constexpr uint32_t kCompactTile = 256;  // pages per compaction tile
+
+// table[hash64] = lowest (origin << 26 | page index); origin 0 parent, 1+r peer r, 15 self
+struct DedupTable {
+  unsigned long long* keys;  // 0 = empty
+  uint32_t* vals;
+  uint64_t mask;  // capacity - 1, capacity a power of two
+};
+
+struct PeerCrcs {
+  const uint32_t* parent;
+  const uint32_t* peer[8];
+};
+
+struct PeerImages {
+  const unsigned char* parent;
+  uint64_t parent_pages;
+  const unsigned char* peer[8];
+  uint64_t peer_pages[8];
+  uint32_t n_peers;
+};
+
+// counters written by the kernels, read back by the host after a sync
+struct DevCounters {
+  unsigned long long kind[5];    // pages per GRIT_KIND_*, filled by compact
+  unsigned long long n_stored;   // pages given a slot by the last compact
+  unsigned long long overflow;   // pages that did not fit capacity_pages
+  unsigned long long n_bad;      // restore: pages that failed
+  unsigned long long first_bad;  // restore: lowest such page
+  unsigned long long slot_base;       // compact, chained mode: first slot of this launch
+  unsigned long long slot_base_next;  // compact: slot_base + pages stored by this launch
+  unsigned int ticket;                // compact: dynamic tile counter
+  unsigned int pad;
+};
+
+struct LaunchGeom {
+  int sm_count;
+};
+
+cudaError_t launch_analyze(const LaunchGeom& g, const Gf2Tables* d_tab, const void* d_image,
+                           uint64_t n_pages, uint32_t* d_crc, uint64_t* d_hash, uint32_t* d_ref,
+                           cudaStream_t s);
+cudaError_t launch_table_insert(const LaunchGeom& g, DedupTable t, const uint64_t* d_hash,
+                                const uint32_t* d_ref_or_null, uint64_t n, uint32_t origin,
+                                uint64_t index_base, cudaStream_t s);
+cudaError_t launch_resolve(const LaunchGeom& g, DedupTable t, uint64_t page0, uint64_t page1, const uint32_t* d_crc,
+                           const uint64_t* d_hash, uint32_t* d_ref, PeerCrcs crcs, cudaStream_t s);
+cudaError_t launch_compact(const LaunchGeom& g, const void* d_image, uint64_t n_pages, uint32_t* d_ref,
+                           void* d_packed, uint64_t capacity_pages, uint64_t slot_base, bool chained,
+                           unsigned long long* d_tile_status, DevCounters* d_cnt, cudaStream_t s);
+cudaError_t launch_restore(const LaunchGeom& g, const Gf2Tables* d_tab, const void* d_packed,
+                           uint64_t n_slots, const uint32_t* d_ref, const uint32_t* d_crc,
+                           uint64_t n_pages, uint64_t page0, uint64_t page1, PeerImages imgs, void* d_out,
+                           int verify, DevCounters* d_cnt, cudaStream_t s);
+cudaError_t launch_synth(const LaunchGeom& g, void* d_image, uint64_t n_pages, uint64_t page_base,
+                         uint64_t seed, uint32_t pct_zero, uint32_t pct_dup, uint32_t dup_pool,
+                         cudaStream_t s);
+
+uint32_t page_kernel_smem_bytes();
+cudaError_t configure_kernels();  // opt in to the large dynamic shared memory, once per device
+
+}  // namespace grit

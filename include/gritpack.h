@@ -1,0 +1,214 @@
+/*
+ * gritpack -- C ABI of libgritpack.so, the B200 (sm_100a) replacement for the
+ * grit-agent data mover.
+ *
+ * The reference moves a pod's checkpoint image directory between the node and
+ * the checkpoint PV with a plain recursive copy:
+ *     pkg/gritagent/copy/copy.go:17   TransferData(ctx, srcDir, dstDir) error
+ *     pkg/gritagent/copy/copy.go:92   CreateSentinelFile(dir, fileName) error
+ * called from pkg/gritagent/checkpoint/checkpoint.go:20 (upload) and
+ * pkg/gritagent/restore/restore.go:16,20 (download, then the sentinel).
+ * It has no cgo, no FFI and no plugin registry: a maintainer swaps the two
+ * calls for the entry points below through the cgo stub in INTEGRATION.md.
+ *
+ * Conventions: every call returns 0 on success and a negative GRIT_E* code on
+ * failure, with a human-readable message copied into err[errlen] when err is
+ * not NULL (the bridge wraps it in errors.New).  Plain pointers and sizes only.
+ * "d_" pointers are CUDA device pointers on the context's device, "h_" are
+ * host pointers.  `stream` is a cudaStream_t passed as void* (NULL = the
+ * context's own stream); calls that return host-visible results synchronise it.
+ */
+#ifndef GRITPACK_H
+#define GRITPACK_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GRIT_ABI_VERSION 1
+#define GRIT_PAGE_SIZE 4096u
+#define GRIT_MAX_PAGES (1u << 26) /* 256 GiB per image; a B200 holds 180 GB */
+#define GRIT_MAX_PEERS 8u
+
+#define GRIT_OK 0
+#define GRIT_EINVAL (-1)  /* bad argument                                      */
+#define GRIT_ECUDA (-2)   /* CUDA runtime error, or no usable sm_100 device    */
+#define GRIT_EIO (-3)     /* file system error                                 */
+#define GRIT_ECRC (-4)    /* restore: a page failed CRC-32C or a bad reference */
+#define GRIT_EFORMAT (-5) /* packed image is not one this library wrote        */
+#define GRIT_ENOMEM (-6)
+
+/* Page reference: kind in bits 31..29, value in bits 28..0. */
+#define GRIT_KIND_ZERO 0u   /* all-zero page, nothing stored                   */
+#define GRIT_KIND_DATA 1u   /* value = slot (4 KiB units) in the packed pages  */
+#define GRIT_KIND_DUP 2u    /* value = earlier page of this image (a DATA page)*/
+#define GRIT_KIND_PARENT 3u /* value = page index in the parent image          */
+#define GRIT_KIND_PEER 4u   /* value = rank << 26 | page index on that rank    */
+#define GRIT_REF_KIND(r) ((uint32_t)(r) >> 29)
+#define GRIT_REF_VALUE(r) ((uint32_t)(r) & 0x1FFFFFFFu)
+
+typedef struct grit_ctx grit_ctx;
+
+/* Per-page hashes of another image this one may refer to. */
+typedef struct grit_table {
+  const uint64_t *hash; /* hash64 per logical page */
+  const uint32_t *crc;  /* CRC-32C per logical page */
+  uint64_t n_pages;
+} grit_table;
+
+typedef struct grit_pack_stats {
+  uint64_t n_pages, n_zero, n_data, n_dup, n_parent, n_peer;
+  double gpu_ms; /* device time of the kernels of this call (CUDA events) */
+} grit_pack_stats;
+
+typedef struct grit_restore_stats {
+  uint64_t n_pages, n_bad, first_bad; /* first_bad = UINT64_MAX when n_bad == 0 */
+  double gpu_ms;
+} grit_restore_stats;
+
+/* Options of the directory-level calls.  Zero-initialise, then set fields. */
+typedef struct grit_opts {
+  uint32_t struct_size; /* sizeof(grit_opts), for ABI growth                   */
+  int32_t device;       /* CUDA device ordinal                                 */
+  uint32_t verify;      /* restore: recompute and compare every page's CRC-32C */
+  uint32_t io_threads;  /* file reader/writer threads, 0 = default (4)         */
+  uint64_t chunk_bytes; /* pipeline chunk, 0 = default (64 MiB)                */
+  const char *parent_dir; /* previous packed checkpoint for incremental, or NULL */
+} grit_opts;
+
+typedef struct grit_stats {
+  uint64_t bytes_logical; /* bytes of the file tree                            */
+  uint64_t bytes_stored;  /* bytes written to (pack) or read from (restore) the PV */
+  uint64_t n_files, n_dirs;
+  uint64_t n_pages, n_zero, n_data, n_dup, n_parent, n_peer, n_bad;
+  double seconds;     /* wall clock of the call                                */
+  double gpu_ms;      /* device time in kernels                                */
+  double h2d_bytes, d2h_bytes;
+} grit_stats;
+
+/* ---- library ---------------------------------------------------------- */
+
+/* GRIT_ABI_VERSION of the loaded library. */
+int grit_version(void);
+
+/* Go: crc32.Update(crc, crc32.MakeTable(crc32.Castagnoli), data).  Host code,
+ * used for manifest checksums; page CRCs are computed on the GPU. */
+uint32_t grit_crc32c(uint32_t crc, const void *data, size_t len);
+
+/* Creates the per-device state (streams, GF(2) tables, scratch).  Fails with
+ * GRIT_ECUDA when the device is missing: there is no CPU fallback.  The
+ * reference keeps no state between calls (copy.go:17-64); a context is the
+ * explicit create/destroy pair SURVEY 8(b) "Ownership" allows. */
+int grit_ctx_create(int device, grit_ctx **out, char *err, size_t errlen);
+void grit_ctx_destroy(grit_ctx *ctx);
+
+/* Number of kernels this context has launched (bench.py's gpu_launches). */
+uint64_t grit_ctx_launches(const grit_ctx *ctx);
+
+/* ---- page kernels on device buffers ----------------------------------
+ * These have no reference counterpart: copy.go:79 (io.Copy) moves opaque
+ * bytes.  They are the new work north_star places behind TransferData. */
+
+/* K1: per 4 KiB page CRC-32C (== Go hash/crc32 Castagnoli of the page),
+ * hash64, and d_ref[p] = 0 (GRIT_KIND_ZERO) for an all-zero page, 0xFFFFFFFF
+ * otherwise.  d_image must be 16-byte aligned. */
+int grit_analyze_pages(grit_ctx *ctx, const void *d_image, uint64_t n_pages,
+                       uint32_t *d_crc, uint64_t *d_hash, uint32_t *d_ref,
+                       void *stream, char *err, size_t errlen);
+
+/* K2: dedup.  Input: the arrays K1 wrote.  Output: d_ref[p] becomes ZERO, DUP,
+ * PARENT, PEER, or 0xFFFFFFFE for a page that must be stored.  The owner of a
+ * hash64 is the lowest (parent, peer rank 0.., this image) x page index; a
+ * page only refers to its owner when the CRC-32C matches too.  parent and
+ * peers[0..n_peers) hold DEVICE pointers; either may be NULL/0. */
+int grit_dedup_pages(grit_ctx *ctx, uint64_t n_pages, const uint32_t *d_crc,
+                     const uint64_t *d_hash, uint32_t *d_ref,
+                     const grit_table *parent, const grit_table *peers,
+                     uint32_t n_peers, void *stream, char *err, size_t errlen);
+
+/* K3: stream compaction.  Pages marked 0xFFFFFFFE get consecutive slots
+ * slot_base, slot_base+1, ... in page order (warp ballot + decoupled look-back
+ * prefix scan) and are copied to d_packed + slot * 4096; d_ref[p] becomes
+ * DATA|slot.  *n_stored receives the number of pages stored. */
+int grit_compact_pages(grit_ctx *ctx, const void *d_image, uint64_t n_pages,
+                       uint32_t *d_ref, void *d_packed, uint64_t capacity_pages,
+                       uint64_t slot_base, uint64_t *n_stored, void *stream,
+                       char *err, size_t errlen);
+
+/* K1+K2+K3 on one device-resident image; the unit bench.py times as `value`. */
+int grit_pack_buffer(grit_ctx *ctx, const void *d_image, uint64_t n_pages,
+                     const grit_table *parent, const grit_table *peers,
+                     uint32_t n_peers, void *d_packed, uint64_t capacity_pages,
+                     uint32_t *d_ref, uint32_t *d_crc, uint64_t *d_hash,
+                     grit_pack_stats *stats, void *stream, char *err,
+                     size_t errlen);
+
+/* K4: inverse scatter.  Every page of d_out is written: zeros, the packed slot,
+ * the owner's slot, or the page of the parent / peer image (device pointers,
+ * fully restored).  With verify != 0 the CRC-32C of every non-zero page is
+ * recomputed from the bytes read and compared with d_crc; mismatches and
+ * references that cannot be followed are counted in stats and make the call
+ * return GRIT_ECRC (d_out is still fully written). */
+int grit_restore_buffer(grit_ctx *ctx, const void *d_packed, uint64_t n_slots,
+                        const uint32_t *d_ref, const uint32_t *d_crc,
+                        uint64_t n_pages, const void *d_parent_image,
+                        uint64_t parent_pages, const void *const *d_peer_images,
+                        const uint64_t *peer_pages, uint32_t n_peers,
+                        void *d_out, int verify, grit_restore_stats *stats,
+                        void *stream, char *err, size_t errlen);
+
+/* K5 (bench/tests only): seeded synthetic image, page classes zero / pool
+ * duplicate / unique; same generator as the oracle's. */
+int grit_synth_image(grit_ctx *ctx, void *d_image, uint64_t n_pages,
+                     uint64_t page_base, uint64_t seed, uint32_t pct_zero,
+                     uint32_t pct_dup, uint32_t dup_pool, void *stream,
+                     char *err, size_t errlen);
+
+/* ---- host buffers through the pinned, double-buffered pipeline --------
+ * What copyFile (copy.go:66-90) is to one file: bytes in host memory in,
+ * bytes in host memory out, H2D and D2H copies overlapped with the kernels.
+ * parent holds HOST pointers here. */
+int grit_pack_host(grit_ctx *ctx, const void *h_image, uint64_t n_pages,
+                   const grit_table *parent, void *h_packed,
+                   uint64_t capacity_pages, uint32_t *h_ref, uint32_t *h_crc,
+                   uint64_t *h_hash, grit_pack_stats *stats, char *err,
+                   size_t errlen);
+int grit_restore_host(grit_ctx *ctx, const void *h_packed, uint64_t n_slots,
+                      const uint32_t *h_ref, const uint32_t *h_crc,
+                      uint64_t n_pages, const void *h_parent_image,
+                      uint64_t parent_pages, void *h_out, int verify,
+                      grit_restore_stats *stats, char *err, size_t errlen);
+/* cudaHostRegister / Unregister of a caller buffer, so that the two calls
+ * above copy at full PCIe rate. */
+int grit_pin_host(void *h_ptr, size_t bytes);
+int grit_unpin_host(void *h_ptr);
+
+/* ---- directories: the drop-in for TransferData ------------------------ */
+
+/* Upload direction of TransferData (checkpoint.go:20): packs the tree under
+ * src_dir into dst_dir on the PV as manifest + page map + unique pages.
+ * Overwrites a previous (partial) pack of the same dst_dir, like os.Create
+ * (copy.go:73); the manifest is written last. */
+int grit_pack_dir(const char *src_dir, const char *dst_dir,
+                  const grit_opts *opts, grit_stats *stats, char *err,
+                  size_t errlen);
+
+/* Download direction of TransferData (restore.go:16): recreates under dst_dir
+ * the tree grit_pack_dir saw -- same relative paths, file bytes and mode bits,
+ * directories 0777 & ~umask (copy.go:36,84-89).  A src_dir without a gritpack
+ * manifest (written by the stock agent) is mirrored file by file.  Does not
+ * write the sentinel. */
+int grit_restore_dir(const char *src_dir, const char *dst_dir,
+                     const grit_opts *opts, grit_stats *stats, char *err,
+                     size_t errlen);
+
+/* CreateSentinelFile (copy.go:92-102): dir/name holding "Transfer Completed\n". */
+int grit_write_sentinel(const char *dir, const char *name);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GRITPACK_H */

@@ -1,0 +1,79 @@
+"""The C-ABI shared library: loads, exports every symbol include/gritpack.h declares, and its
+GPU-free entry points behave.  No compute call is made here (this file runs without a GPU)."""
+import ctypes as C
+import json
+import os
+import re
+
+import pytest
+
+from grit_b200 import _lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_functions():
+    text = open(os.path.join(ROOT, "include", "gritpack.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(grit_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    lib = _lib.load()
+    names = declared_functions()
+    assert "grit_pack_dir" in names and "grit_restore_dir" in names and len(names) >= 15
+    for n in names:
+        assert hasattr(lib, n), f"{n} is declared in include/gritpack.h but not exported"
+    assert set(names) == set(_lib.SYMBOLS), "python binding and header disagree"
+    assert lib.grit_version() == 1
+
+
+def test_host_crc32c_matches_go_golden_vectors():
+    lib = _lib.load()
+    kat = json.load(open(os.path.join(ROOT, "tests", "golden", "crc32c_kat.json")))
+    for s, want in kat["ascii"].items():
+        b = s.encode()
+        assert lib.grit_crc32c(0, b, len(b)) == int(want, 16)
+    b = bytes(4096)
+    assert lib.grit_crc32c(0, b, 4096) == 0x98F94189
+    data = bytes(range(256)) * 9
+    assert lib.grit_crc32c(lib.grit_crc32c(0, data[:1001], 1001), data[1001:], len(data) - 1001) == \
+        lib.grit_crc32c(0, data, len(data))
+
+
+def test_host_crc32c_matches_oracle(oracle):
+    import numpy as np
+    lib = _lib.load()
+    rng = np.random.default_rng(3)
+    for n in (0, 1, 7, 8, 9, 63, 4095, 4096, 4097, 100003):
+        b = rng.integers(0, 256, n, dtype=np.uint8).tobytes()
+        assert lib.grit_crc32c(0, b, n) == oracle.crc32c(b)
+
+
+def test_sentinel_matches_reference_payload(tmp_path):
+    from grit_b200 import copy
+    copy.CreateSentinelFile(str(tmp_path), "download-state")
+    assert (tmp_path / "download-state").read_bytes() == b"Transfer Completed\n"
+    with pytest.raises(_lib.GritError):
+        copy.CreateSentinelFile(str(tmp_path / "missing"), "download-state")
+
+
+def test_no_cpu_fallback_without_a_device():
+    """Without a usable GPU the product must fail loudly, never compute on the CPU."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    h, err = C.c_void_p(), _lib.errbuf()
+    rc = _lib.load().grit_ctx_create(0, C.byref(h), err, len(err))
+    assert rc == _lib.ECUDA and b"no CPU path" in err.value
+    from grit_b200 import copy
+    with pytest.raises(_lib.GritError):
+        copy.TransferData("/tmp", "/tmp/x-never", copy.UPLOAD)
+
+
+def test_product_never_imports_the_oracle():
+    for d, _, files in os.walk(os.path.join(ROOT, "grit_b200")):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cpp", ".h", ".cuh")):
+                text = open(os.path.join(d, f), errors="replace").read()
+                assert "oracle" not in text.lower(), f"{f} mentions the oracle"

@@ -1,0 +1,124 @@
+"""-m gpu: host buffers through the pinned double-buffered pipeline, and whole directories (the TransferData drop-in)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import PAGE, make_criu_tree, mixed_image, tree_snapshot
+
+pytestmark = pytest.mark.gpu
+
+
+def u32(t):
+    return t.numpy().view(np.uint32)
+
+
+@pytest.mark.parametrize("pinned", [True, False])
+@pytest.mark.parametrize("n_pages", [1, 1000, 40000])     # 40000 pages = 3 pipeline chunks of 64 MiB
+def test_pack_host_matches_oracle(ctx, oracle, pinned, n_pages):
+    img = mixed_image(oracle, n_pages, seed=n_pages + 1)
+    t = torch.from_numpy(img)
+    packed = torch.empty(n_pages * PAGE, dtype=torch.uint8)
+    if pinned:
+        t, packed = t.pin_memory(), packed.pin_memory()
+    r = ctx.pack_host(t, packed=packed)
+    o = oracle.pack(img, threads=8)
+    assert {k: v for k, v in r["stats"].items() if k != "gpu_ms"} == o["stats"]
+    assert np.array_equal(u32(r["ref"]), o["ref"]) and np.array_equal(u32(r["crc"]), o["crc"])
+    assert np.array_equal(r["packed"].numpy(), o["packed"])
+    out = torch.empty(n_pages * PAGE, dtype=torch.uint8)
+    if pinned:
+        out = out.pin_memory()
+    out, rs = ctx.restore_host(r["packed"], r["ref"], r["crc"], out=out)
+    assert rs["n_bad"] == 0 and np.array_equal(out.numpy(), img)
+
+
+def test_pack_host_incremental(ctx, oracle):
+    base = mixed_image(oracle, 20000, seed=4)
+    pb = ctx.pack_host(torch.from_numpy(base).pin_memory())
+    child = base.copy()
+    rng = np.random.default_rng(1)
+    for d in rng.choice(20000, 1000, replace=False):
+        child[d * PAGE:(d + 1) * PAGE] = rng.integers(0, 256, PAGE, dtype=np.uint8)
+    r = ctx.pack_host(torch.from_numpy(child).pin_memory(), parent=(pb["hash"], pb["crc"]))
+    o = oracle.pack(child, parent=(pb["hash"].numpy().view(np.uint64), u32(pb["crc"])))
+    assert np.array_equal(u32(r["ref"]), o["ref"]) and r["stats"]["n_data"] == 1000
+    out, rs = ctx.restore_host(r["packed"], r["ref"], r["crc"], parent_image=torch.from_numpy(base))
+    assert rs["n_bad"] == 0 and np.array_equal(out.numpy(), child)
+
+
+def test_restore_host_detects_corruption(ctx, oracle):
+    img = mixed_image(oracle, 30000, seed=6, pct_zero=0, pct_dup=0)
+    r = ctx.pack_host(torch.from_numpy(img))
+    packed = r["packed"].clone()
+    packed[20000 * PAGE + 1] ^= 0xFF
+    out, rs = ctx.restore_host(packed, r["ref"], r["crc"], check=False)
+    assert rs["n_bad"] == 1 and rs["first_bad"] == 20000
+
+
+def test_directory_round_trip_equals_reference_copy(oracle, tmp_path):
+    """restore_dir(pack_dir(D)) must leave what TransferData(TransferData(D)) leaves."""
+    from grit_b200 import agent, copy
+    src, pv, host, ref_pv, ref_host = (tmp_path / n for n in ("src", "pv/ns/ckpt", "host/ns/ckpt", "refpv", "refhost"))
+    src.mkdir()
+    make_criu_tree(str(src), oracle, big_pages=20000)     # > 64 MiB: several pipeline chunks
+    st = agent.RunCheckpoint(agent.GritAgentOptions("checkpoint", str(src), str(pv)))
+    assert st["n_files"] == 11 and st["n_zero"] > 0 and st["n_dup"] > 0 and st["bytes_stored"] < st["bytes_logical"]
+    assert (pv / "gritpack.manifest").exists()
+    st2 = agent.RunRestore(agent.GritAgentOptions("restore", str(pv), str(host)))
+    assert st2["n_bad"] == 0
+    # the reference path, restated: copy up, copy down, sentinel
+    assert oracle.transfer_data(str(src), str(ref_pv))[0] == 0
+    assert oracle.transfer_data(str(ref_pv), str(ref_host))[0] == 0
+    assert oracle.create_sentinel_file(str(ref_host), "download-state") == 0
+    assert tree_snapshot(str(host)) == tree_snapshot(str(ref_host))
+    assert (host / "download-state").read_bytes() == b"Transfer Completed\n"
+
+
+def test_directory_incremental_and_rerun(oracle, tmp_path):
+    from grit_b200 import copy
+    src, pv1, pv2, host = (tmp_path / n for n in ("src", "pv/c1", "pv/c2", "host"))
+    src.mkdir()
+    make_criu_tree(str(src), oracle, big_pages=3000)
+    copy.TransferData(str(src), str(pv1), copy.UPLOAD)
+    # dirty a few pages of the big file, then an incremental upload against c1
+    with open(src / "main/checkpoint/pages-1.img", "r+b") as f:
+        for p in (5, 77, 1500):
+            f.seek(p * PAGE)
+            f.write(os.urandom(PAGE))
+    st = copy.TransferData(str(src), str(pv2), copy.UPLOAD, parent_dir=str(pv1))
+    assert st["n_parent"] > 0 and st["n_data"] <= 3 + 2
+    # a Job retry packs again over the same destination (copy.go:73 truncates)
+    st_again = copy.TransferData(str(src), str(pv2), copy.UPLOAD, parent_dir=str(pv1))
+    assert st_again["n_data"] == st["n_data"]
+    copy.TransferData(str(pv2), str(host), copy.DOWNLOAD)
+    assert tree_snapshot(str(host)) == tree_snapshot(str(src))
+
+
+def test_restore_dir_refuses_incomplete_or_corrupt_images(oracle, tmp_path):
+    from grit_b200 import _lib, copy
+    src, pv, host = tmp_path / "src", tmp_path / "pv", tmp_path / "host"
+    src.mkdir()
+    make_criu_tree(str(src), oracle, big_pages=500)
+    copy.TransferData(str(src), str(pv), copy.UPLOAD)
+    with open(pv / "pages.bin", "r+b") as f:
+        f.seek(40 * PAGE + 3)
+        f.write(b"\xAA\xBB")
+    with pytest.raises(_lib.GritError) as e:
+        copy.TransferData(str(pv), str(host), copy.DOWNLOAD)
+    assert e.value.code == _lib.ECRC
+    os.remove(pv / "gritpack.manifest")
+    with pytest.raises(_lib.GritError) as e:
+        copy.TransferData(str(pv), str(host), copy.DOWNLOAD)
+    assert e.value.code == _lib.EFORMAT
+
+
+def test_empty_directory(tmp_path):
+    from grit_b200 import copy
+    src, pv, host = tmp_path / "src", tmp_path / "pv", tmp_path / "host"
+    (src / "a" / "b").mkdir(parents=True)
+    (src / "a" / "empty").write_bytes(b"")
+    copy.TransferData(str(src), str(pv), copy.UPLOAD)
+    copy.TransferData(str(pv), str(host), copy.DOWNLOAD)
+    assert tree_snapshot(str(host)) == tree_snapshot(str(src))
