@@ -55,7 +55,9 @@ int read_counters(grit_ctx* ctx, cudaStream_t s, char* err, size_t errlen) {
 
 namespace {
 
-cudaStream_t pick(grit_ctx* ctx, void* stream) { return stream ? static_cast<cudaStream_t>(stream) : ctx->stream; }
+// `stream` is the caller's cudaStream_t; NULL is the CUDA default stream, as everywhere in the runtime API,
+// so work is ordered after whatever the caller enqueued there (the inputs' producers).
+cudaStream_t pick(grit_ctx*, void* stream) { return static_cast<cudaStream_t>(stream); }
 
 int enter(grit_ctx* ctx, char* err, size_t errlen) {
   if (!ctx) return fail(err, errlen, GRIT_EINVAL, "null context");

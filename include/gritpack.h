@@ -15,8 +15,9 @@
  * failure, with a human-readable message copied into err[errlen] when err is
  * not NULL (the bridge wraps it in errors.New).  Plain pointers and sizes only.
  * "d_" pointers are CUDA device pointers on the context's device, "h_" are
- * host pointers.  `stream` is a cudaStream_t passed as void* (NULL = the
- * context's own stream); calls that return host-visible results synchronise it.
+ * host pointers.  `stream` is a cudaStream_t passed as void* (NULL = the CUDA
+ * default stream): the kernels are ordered after the work already enqueued on
+ * it; calls that return host-visible results synchronise it before returning.
  */
 #ifndef GRITPACK_H
 #define GRITPACK_H

@@ -186,3 +186,15 @@ def test_full_size_round_trip_properties(ctx):
     del img
     r2 = ctx.pack(out)
     assert torch.equal(r2["ref"], ref) and torch.equal(r2["crc"], r["crc"]) and torch.equal(r2["packed"], r["packed"])
+
+
+def test_calls_are_ordered_on_the_callers_stream(ctx, oracle):
+    """The image's producer and the pack run on the same (non-default) stream without a host sync in between."""
+    s = torch.cuda.Stream()
+    big = torch.empty(64 << 20, dtype=torch.uint8, device="cuda")
+    for i in range(3):
+        with torch.cuda.stream(s):
+            big.random_(0, 256)                      # still running when pack is enqueued
+            r = ctx.pack(big)
+            out, rs = ctx.restore(r["packed"], r["ref"], r["crc"])
+            assert rs["n_bad"] == 0 and torch.equal(out, big)
