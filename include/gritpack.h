@@ -139,6 +139,33 @@ int grit_compact_pages(grit_ctx *ctx, const void *d_image, uint64_t n_pages,
                        uint64_t slot_base, uint64_t *n_stored, void *stream,
                        char *err, size_t errlen);
 
+/* K3 for callers that must not allocate.  It has no counterpart in the reference.
+ * Same inputs, outputs and results as grit_compact_pages, but no grit_ctx and no
+ * cudaMalloc, cudaMallocHost or cudaFree, on any call: the scan's working memory
+ * (one status word per 256-page tile plus a counter block, 129 KiB in all) is a
+ * fixed array inside the library image, present on every GPU that loads the
+ * library until the process exits.  Meant for a packer that runs while the
+ * checkpointed job's allocator holds nearly all of HBM (an allocation could
+ * fail, or force that allocator to give memory back), for callers that cannot
+ * take the device-wide synchronisation cudaMalloc/cudaFree imply, and for host
+ * runtimes that hand out a fixed set of buffers and forbid more.
+ *   - n_pages above GRIT_STATIC_MAX_PAGES (16 GiB of image) is refused with
+ *     GRIT_EINVAL; use grit_compact_pages for larger images.
+ *   - The first call on a device looks up the array's device address
+ *     (cudaGetSymbolAddress) and reads two device attributes; make that first
+ *     call before starting any stream capture.
+ *   - All calls on a device share the one array.  Each call clears what it needs
+ *     on `stream` before the kernel, so calls issued one after another are
+ *     independent; two calls whose GPU work overlaps (different streams or
+ *     threads) race on it and give wrong results -- serialise them.
+ *   - Synchronises `stream` before returning (to report *n_stored). */
+#define GRIT_STATIC_MAX_PAGES (1u << 22)
+int grit_compact_pages_static(int device, const void *d_image, uint64_t n_pages,
+                              uint32_t *d_ref, void *d_packed,
+                              uint64_t capacity_pages, uint64_t slot_base,
+                              uint64_t *n_stored, void *stream, char *err,
+                              size_t errlen);
+
 /* K1+K2+K3 on one device-resident image; the unit bench.py times as `value`. */
 int grit_pack_buffer(grit_ctx *ctx, const void *d_image, uint64_t n_pages,
                      const grit_table *parent, const grit_table *peers,
