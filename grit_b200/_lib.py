@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libgritpack.so")
+LIB_PATH = os.environ.get("GRITPACK_LIB") or os.path.join(_HERE, "csrc", "libgritpack.so")  # override: kernel A/B builds
 
 PAGE = 4096
 MAX_PAGES = 1 << 26

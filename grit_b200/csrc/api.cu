@@ -1,5 +1,7 @@
 // C ABI over the page kernels: context, stage entry points, pack/restore of a
 // device-resident image.  Declarations and reference citations: include/gritpack.h.
+#include <algorithm>
+#include <cstdlib>
 #include <new>
 
 #include "ctx.h"
@@ -28,7 +30,8 @@ int ensure_table(grit_ctx* ctx, uint64_t n_items, DedupTable* t, char* err, size
 }
 
 int ensure_status(grit_ctx* ctx, uint64_t n_pages, char* err, size_t errlen) {
-  const uint64_t tiles = (n_pages + kCompactTile - 1) / kCompactTile + 1;
+  const uint64_t tile = std::min<uint64_t>(kCompactTile, fused_tile_pages());
+  const uint64_t tiles = (n_pages + tile - 1) / tile + 1;
   if (tiles > ctx->status_cap) {
     if (ctx->d_status) cudaFree(ctx->d_status);
     ctx->d_status = nullptr;
@@ -49,6 +52,17 @@ int read_counters(grit_ctx* ctx, cudaStream_t s, char* err, size_t errlen) {
   GRIT_CUDA(cudaMemcpyAsync(ctx->h_cnt, ctx->d_cnt, sizeof(DevCounters), cudaMemcpyDeviceToHost, s));
   GRIT_CUDA(cudaStreamSynchronize(s));
   return GRIT_OK;
+}
+
+// The pack runs K1, K2, K3 as three kernels (DRAM traffic N + 2U).  GRITPACK_FUSED=1 selects the
+// experimental single-pass kernel (k_pack_fused, N + U when its re-reads hit L2); on B200 it is
+// currently slower, so it is opt-in.
+bool staged_pack() {
+  static const bool v = [] {
+    const char* e = getenv("GRITPACK_FUSED");
+    return !(e && *e && *e != '0');
+  }();
+  return v;
 }
 
 }  // namespace grit
@@ -74,7 +88,7 @@ int check_pages(uint64_t n_pages, const void* p, char* err, size_t errlen) {
 // table build + resolve, asynchronous on s
 int dedup_async(grit_ctx* ctx, uint64_t n_pages, const uint32_t* d_crc, const uint64_t* d_hash, uint32_t* d_ref,
                 const grit_table* parent, const grit_table* peers, uint32_t n_peers, cudaStream_t s, char* err,
-                size_t errlen) {
+                size_t errlen, DedupTable* table_out = nullptr, PeerCrcs* crcs_out = nullptr) {
   if (n_peers > GRIT_MAX_PEERS) return fail(err, errlen, GRIT_EINVAL, "n_peers %u > %u", n_peers, GRIT_MAX_PEERS);
   uint64_t items = n_pages;
   PeerCrcs crcs{};
@@ -101,6 +115,11 @@ int dedup_async(grit_ctx* ctx, uint64_t n_pages, const uint32_t* d_crc, const ui
       GRIT_CUDA(launch_table_insert(ctx->geom, t, peers[r].hash, nullptr, peers[r].n_pages, 1 + r, 0, s));
       ctx->launches++;
     }
+  if (table_out) {  // the fused kernel inserts and resolves this image's own pages itself
+    *table_out = t;
+    *crcs_out = crcs;
+    return GRIT_OK;
+  }
   GRIT_CUDA(launch_table_insert(ctx->geom, t, d_hash, d_ref, n_pages, kOriginSelf, 0, s));
   GRIT_CUDA(launch_resolve(ctx->geom, t, 0, n_pages, d_crc, d_hash, d_ref, crcs, s));
   ctx->launches += 2;
@@ -246,10 +265,22 @@ int grit_pack_buffer(grit_ctx* ctx, const void* d_image, uint64_t n_pages, const
   cudaStream_t s = pick(ctx, stream);
   if (int rc = reset_counters(ctx, s, err, errlen)) return rc;
   GRIT_CUDA(cudaEventRecord(ctx->ev0, s));
-  GRIT_CUDA(launch_analyze(ctx->geom, ctx->d_tables, d_image, n_pages, d_crc, d_hash, d_ref, s));
-  ctx->launches++;
-  if (int rc = dedup_async(ctx, n_pages, d_crc, d_hash, d_ref, parent, peers, n_peers, s, err, errlen)) return rc;
-  if (int rc = compact_async(ctx, d_image, n_pages, d_ref, d_packed, capacity_pages, 0, s, err, errlen)) return rc;
+  if (staged_pack()) {  // K1, K2, K3 as separate kernels
+    GRIT_CUDA(launch_analyze(ctx->geom, ctx->d_tables, d_image, n_pages, d_crc, d_hash, d_ref, s));
+    ctx->launches++;
+    if (int rc = dedup_async(ctx, n_pages, d_crc, d_hash, d_ref, parent, peers, n_peers, s, err, errlen)) return rc;
+    if (int rc = compact_async(ctx, d_image, n_pages, d_ref, d_packed, capacity_pages, 0, s, err, errlen)) return rc;
+  } else if (n_pages) {
+    DedupTable t{};
+    PeerCrcs crcs{};
+    if (int rc = dedup_async(ctx, n_pages, d_crc, d_hash, d_ref, parent, peers, n_peers, s, err, errlen, &t, &crcs)) return rc;
+    if (int rc = ensure_status(ctx, n_pages, err, errlen)) return rc;
+    const uint64_t tiles = (n_pages + fused_tile_pages() - 1) / fused_tile_pages();
+    GRIT_CUDA(cudaMemsetAsync(ctx->d_status, 0, tiles * sizeof(unsigned long long), s));
+    GRIT_CUDA(launch_pack_fused(ctx->geom, ctx->d_tables, d_image, n_pages, 0, d_crc, d_hash, d_ref, t, crcs, d_packed,
+                                capacity_pages, 0, false, ctx->d_status, ctx->d_cnt, s));
+    ctx->launches++;
+  }
   GRIT_CUDA(cudaEventRecord(ctx->ev1, s));
   if (int rc = read_counters(ctx, s, err, errlen)) return rc;
   const DevCounters& c = *ctx->h_cnt;

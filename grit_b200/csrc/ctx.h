@@ -55,5 +55,6 @@ int ensure_table(grit_ctx* ctx, uint64_t n_items, DedupTable* t, char* err, size
 int ensure_status(grit_ctx* ctx, uint64_t n_pages, char* err, size_t errlen);
 int reset_counters(grit_ctx* ctx, cudaStream_t s, char* err, size_t errlen);
 int read_counters(grit_ctx* ctx, cudaStream_t s, char* err, size_t errlen);  // syncs s
+bool staged_pack();  // true unless GRITPACK_FUSED=1 selects the experimental single-pass pack kernel
 
 }  // namespace grit

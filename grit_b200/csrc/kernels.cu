@@ -9,6 +9,8 @@
 // defines the work; gf2_tables.h explains the CRC algebra.
 #include "kernels.h"
 
+#include <type_traits>
+
 namespace grit {
 
 extern __shared__ __align__(1024) unsigned char smem[];
@@ -65,6 +67,32 @@ __device__ __forceinline__ uint4 ldg_stream(const uint4* p) {
 __device__ __forceinline__ void stg_stream(uint4* p, const uint4& v) {
   asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y),
                "r"(v.z), "r"(v.w)
+               : "memory");
+}
+
+// L2 eviction policies (descriptor constants after compilation).  The fused pack reads every tile
+// twice: the first read asks L2 to keep the lines (evict_last), the second read and all streamed
+// writes mark theirs evict_first, so the tiles in flight, not the data already done with, own L2.
+__device__ __forceinline__ uint64_t policy_evict_last() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ uint64_t policy_evict_first() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ uint4 ldg_hint(const uint4* p, uint64_t pol) {
+  uint4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(p), "l"(pol));
+  return v;
+}
+__device__ __forceinline__ void stg_hint(uint4* p, const uint4& v, uint64_t pol) {
+  asm volatile("st.global.L1::no_allocate.L2::cache_hint.v4.u32 [%0], {%1,%2,%3,%4}, %5;" ::"l"(p), "r"(v.x),
+               "r"(v.y), "r"(v.z), "r"(v.w), "l"(pol)
                : "memory");
 }
 
@@ -132,6 +160,51 @@ __device__ __forceinline__ void absorb(PageAcc& a, const uint4& v, uint32_t lane
   }
 }
 
+// compile-time loop: f(std::integral_constant<int, J>) for J = A .. B-1
+template <int A, int B, class F>
+__device__ __forceinline__ void static_for(F&& f) {
+  if constexpr (A < B) {
+    f(std::integral_constant<int, A>{});
+    static_for<A + 1, B>(f);
+  }
+}
+
+constexpr int kRing = 16;  // 16-byte loads each lane keeps in flight (half a page per 8-lane group)
+
+template <bool kHint>
+__device__ __forceinline__ uint4 ldg_or_zero(const uint4* p, bool on, uint64_t pol) {
+  if (!on) return make_uint4(0, 0, 0, 0);
+  return kHint ? ldg_hint(p, pol) : ldg_stream(p);
+}
+
+template <bool kHint = false, int KR>
+__device__ __forceinline__ void ring_fill(uint4 (&ring)[KR], const uint4* src, bool on, uint64_t pol = 0) {
+#pragma unroll
+  for (int j = 0; j < KR; j++) ring[j] = ldg_or_zero<kHint>(src + 8 * j, on, pol);
+}
+
+// One page per 8-lane group, 32 steps of 16 bytes per lane.  On entry `ring` holds
+// steps 0..15 of the current page; every step consumes one slot and immediately
+// refills it with the load 16 steps ahead (the second half of this page, then the
+// first half of `next`), so 15 loads per lane stay in flight throughout.  On exit
+// `ring` holds steps 0..15 of `next`.  sink(j, v) sees every 16-byte value in order.
+template <bool kCrc, bool kHash, bool kHint = false, int KR, class Sink>
+__device__ __forceinline__ void page_pass(PageAcc& a, uint4 (&ring)[KR], const uint4* cur, bool cur_on,
+                                          const uint4* next, bool next_on, uint32_t lane4, Sink&& sink,
+                                          uint64_t pol = 0) {
+  static_for<0, 32>([&](auto jc) {
+    constexpr int j = decltype(jc)::value;
+    const uint4 v = ring[j % KR];
+    if (j < 32 - KR) ring[j % KR] = ldg_or_zero<kHint>(cur + 8 * (j + KR), cur_on, pol);
+    else ring[j % KR] = ldg_or_zero<kHint>(next + 8 * (j + KR - 32), next_on, pol);
+    sink(jc, v);
+    if (kHash && j % 8 == 0 && j > 0) a.h *= kGold;
+    if (kCrc) absorb<j % 8, j == 0, kHash>(a, v, lane4);
+  });
+}
+
+// Eight 16-byte steps at a time, for kernels that also store (K4): loads and stores go out in
+// bursts of eight per lane, which DRAM serves better than a load/store pair per step.
 template <bool kFirstBatch, bool kHash>
 __device__ __forceinline__ void absorb_batch(PageAcc& a, const uint4 (&v)[8], uint32_t lane4) {
   if (kHash && !kFirstBatch) a.h *= kGold;
@@ -143,6 +216,11 @@ __device__ __forceinline__ void absorb_batch(PageAcc& a, const uint4 (&v)[8], ui
   absorb<5, false, kHash>(a, v[5], lane4);
   absorb<6, false, kHash>(a, v[6], lane4);
   absorb<7, false, kHash>(a, v[7], lane4);
+}
+
+__device__ __forceinline__ void load_batch(uint4 (&v)[8], const uint4* src, bool on) {
+#pragma unroll
+  for (int j = 0; j < 8; j++) v[j] = on ? ldg_stream(src + 8 * j) : make_uint4(0, 0, 0, 0);
 }
 
 // Fold the lane's four chains, weight by the lane's position, XOR over the
@@ -168,11 +246,6 @@ __device__ __forceinline__ unsigned long long finish_hash(const PageAcc& a, uint
   return v ? v : 1ull;
 }
 
-__device__ __forceinline__ void load_batch(uint4 (&v)[8], const uint4* src, bool on) {
-#pragma unroll
-  for (int j = 0; j < 8; j++) v[j] = on ? ldg_stream(src + 8 * j) : make_uint4(0, 0, 0, 0);
-}
-
 // ------------------------------------------------------------------ K1 analyze
 // A warp takes four consecutive pages per step; lanes 8g..8g+7 own page g.
 __global__ void __launch_bounds__(kThreads, 1)
@@ -186,26 +259,19 @@ k_analyze(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ image, u
   uint64_t grp = (uint64_t)blockIdx.x * kWarps + warp;
   if (grp >= n_groups) return;
 
-  uint4 cur[8], nxt[8];
+  uint4 ring[kRing];
   uint64_t p = 4 * grp + g;
   const uint4* src = image + p * 256 + l;
-  load_batch(cur, src, p < n_pages);
+  ring_fill(ring, src, p < n_pages);
   for (; grp < n_groups; grp += stride) {
     PageAcc a;
     a.z = 0;
     a.h = 0;
     const bool on = p < n_pages;
-    load_batch(nxt, src + 64, on);
-    absorb_batch<true, true>(a, cur, lane4);
-    load_batch(cur, src + 128, on);
-    absorb_batch<false, true>(a, nxt, lane4);
-    load_batch(nxt, src + 192, on);
-    absorb_batch<false, true>(a, cur, lane4);
-    // prefetch the first batch of this warp's next group
-    const uint64_t p_next = 4 * (grp + stride) + g;
+    const uint64_t p_next = 4 * (grp + stride) + g;  // this warp's next group: prefetched across the boundary
     const uint4* src_next = image + p_next * 256 + l;
-    load_batch(cur, src_next, (grp + stride < n_groups) && p_next < n_pages);
-    absorb_batch<false, true>(a, nxt, lane4);
+    const bool next_on = (grp + stride < n_groups) && p_next < n_pages;
+    page_pass<true, true>(a, ring, src, on, src_next, next_on, lane4, [](auto, const uint4&) {});
 
     const uint32_t page_crc = finish_crc(a, l);
     uint32_t z = a.z;
@@ -398,7 +464,272 @@ k_compact(const uint4* __restrict__ image, uint64_t n_pages, uint32_t* __restric
   }
 }
 
+// ------------------------------------------------------------------ K1+K2+K3 fused
+// One pass over the image.  The sixteen warps of a CTA form kGroups independent groups that share
+// the CRC tables; each group takes tiles by ticket and runs, per tile,
+//   A  analyze the pages (HBM -> registers, lines kept in L2), write crc/hash, enter non-zero
+//      hashes in the table
+//   B  publish INSERTED; wait until every earlier tile has inserted too (then the table's minimum
+//      for each of this tile's hashes is final); decide each page's reference; publish the number
+//      of pages to store; decoupled look-back over earlier tiles for the tile's first slot
+//   C  copy the pages to store into the packed image -- read microseconds ago, so these reads hit
+//      L2 and DRAM sees the image once (N read + U written).
+// Groups only synchronise within themselves (named barriers), so on every SM the waits and copies
+// of one group overlap the CRC arithmetic of the others.  All waits are on lower tile numbers,
+// ticketed earlier by groups that are resident (grid <= SM count, one CTA per SM), so they end.
+#ifndef GRIT_FUSED_GROUPS
+#define GRIT_FUSED_GROUPS 2
+#endif
+#ifndef GRIT_FUSED_ROUNDS
+#define GRIT_FUSED_ROUNDS 2
+#endif
+constexpr int kGroups = GRIT_FUSED_GROUPS;
+constexpr int kGroupWarps = kWarps / kGroups;
+constexpr int kGroupThreads = kGroupWarps * 32;
+constexpr int kFusedRounds = GRIT_FUSED_ROUNDS;
+constexpr int kFusedTile = kGroupWarps * 4 * kFusedRounds;  // pages per group tile
+constexpr int kTileWarps = (kFusedTile + 31) / 32;          // warps that hold one page per lane in B
+static_assert(kFusedTile <= kGroupThreads, "one thread per page in the resolve step");
+constexpr unsigned long long kStInserted = 1ull << 62, kStAgg = 2ull << 62, kStPrefix = 3ull << 62;
+constexpr uint32_t kTsZero = 0xFFFFFFFFu, kTsAbsent = 0xFFFFFFFEu;
+
+__device__ __forceinline__ uint32_t ld_cg_u32(const uint32_t* p) { return __ldcg(p); }
+__device__ __forceinline__ void group_sync(uint32_t grp) {
+  asm volatile("bar.sync %0, %1;" ::"r"(grp + 1), "r"(kGroupThreads) : "memory");
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+k_pack_fused(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ image, uint64_t n_pages, uint64_t page0,
+             uint32_t* __restrict__ crc, unsigned long long* __restrict__ hash, uint32_t* __restrict__ ref,
+             DedupTable t, PeerCrcs crcs, uint4* __restrict__ packed, uint64_t capacity_pages, uint64_t slot_base,
+             int chained, unsigned long long* __restrict__ status, DevCounters* __restrict__ cnt) {
+  __shared__ uint32_t s_tile[kGroups][2], s_excl[kGroups], s_warp_cnt[kGroups][kTileWarps], s_ts[kGroups][kFusedTile];
+  __shared__ uint16_t s_list[kGroups][kFusedTile];
+  load_tables(tabs);
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t grp = warp / kGroupWarps, gw = warp % kGroupWarps, gt = threadIdx.x - grp * kGroupThreads;
+  const uint32_t g = lane >> 3, l = lane & 7, lane4 = lane * 4;
+  const uint32_t n_tiles = (uint32_t)((n_pages + kFusedTile - 1) / kFusedTile);
+  const uint64_t ref_base = chained ? cnt->slot_base : slot_base;
+  const uint64_t out_base = chained ? 0 : slot_base;
+  const uint64_t keep_in_l2 = policy_evict_last(), done_with = policy_evict_first();
+  uint32_t n_kind[5] = {0, 0, 0, 0, 0};  // this thread's page counts per kind
+
+  if (gt == 0) s_tile[grp][0] = atomicAdd(&cnt->ticket, 1u);
+  group_sync(grp);
+  uint32_t tile = s_tile[grp][0];
+  uint4 ring[kRing];
+  if (tile < n_tiles) {
+    const uint64_t p = (uint64_t)tile * kFusedTile + gw * 4 + g;
+    ring_fill<true>(ring, image + p * 256 + l, p < n_pages, keep_in_l2);
+  }
+  for (uint32_t it = 1; tile < n_tiles; it++) {
+    // the next ticket is taken now so that the load ring can run on into the next tile
+    if (gt == 0) s_tile[grp][it & 1] = atomicAdd(&cnt->ticket, 1u);
+    group_sync(grp);
+    const uint32_t next_tile = s_tile[grp][it & 1];
+    const uint64_t base = (uint64_t)tile * kFusedTile;  // first page of the tile, chunk-local
+
+    // ---- A: analyze + insert
+    static_for<0, kFusedRounds>([&](auto rc) {
+      constexpr int r = decltype(rc)::value;
+      const uint64_t p = base + r * (kGroupWarps * 4) + gw * 4 + g;
+      const bool on = p < n_pages;
+      const uint64_t p_next = (r + 1 < kFusedRounds) ? p + kGroupWarps * 4 : (uint64_t)next_tile * kFusedTile + gw * 4 + g;
+      const bool next_on = ((r + 1 < kFusedRounds) || next_tile < n_tiles) && p_next < n_pages;
+      PageAcc a;
+      a.z = 0;
+      a.h = 0;
+      page_pass<true, true, true>(a, ring, image + p * 256 + l, on, image + p_next * 256 + l, next_on, lane4,
+                                  [](auto, const uint4&) {}, keep_in_l2);
+      const uint32_t page_crc = finish_crc(a, l);
+      uint32_t z = a.z;
+      z |= __shfl_xor_sync(0xFFFFFFFFu, z, 1);
+      z |= __shfl_xor_sync(0xFFFFFFFFu, z, 2);
+      z |= __shfl_xor_sync(0xFFFFFFFFu, z, 4);
+      const unsigned long long h = finish_hash(a, l);
+      if (l == 0) {
+        uint32_t ts = kTsAbsent;
+        if (on) {
+          const uint64_t gp = page0 + p;
+          crc[gp] = page_crc;
+          hash[gp] = h;
+          ts = kTsZero;
+          if (z) {
+            const uint32_t v = kOriginSelf << 26 | (uint32_t)gp;
+            uint64_t sl = table_home(h, t.mask);
+            for (;; sl = (sl + 1) & t.mask) {
+              unsigned long long k = t.keys[sl];
+              if (k == 0ull) k = atomicCAS(&t.keys[sl], 0ull, h);
+              if (k == 0ull || k == h) {
+                atomicMin(&t.vals[sl], v);
+                break;
+              }
+            }
+            ts = (uint32_t)sl;
+          }
+        }
+        s_ts[grp][(uint32_t)(p - base)] = ts;
+      }
+    });
+    __threadfence();  // crc/hash stores and table atomics before the group's flag
+    group_sync(grp);
+
+    // ---- B: ordering with earlier tiles, references, slots
+    if (gw == 0) {
+      if (lane == 0) st_status(&status[tile], kStInserted);
+      for (int64_t look = (int64_t)tile - 1; look >= 0; look -= 32) {
+        const int64_t idx = look - lane;
+        unsigned long long st;
+        do {
+          st = idx >= 0 ? ld_status(&status[idx]) : kStPrefix;
+        } while (__any_sync(0xFFFFFFFFu, (st >> 62) == 0));
+        if (__any_sync(0xFFFFFFFFu, (st >> 62) == 3)) break;  // everything below a PREFIX tile has inserted
+      }
+      __threadfence();
+    }
+    group_sync(grp);
+
+    uint32_t kind = 7u;  // 7 = no page
+    bool keep = false;
+    uint64_t gp = 0;
+    if (gt < (uint32_t)kFusedTile) {
+      const uint32_t ts = s_ts[grp][gt];
+      gp = page0 + base + gt;
+      if (ts == kTsZero) {
+        kind = 0u;
+        ref[gp] = 0u;
+      } else if (ts != kTsAbsent) {
+        const uint32_t v = ld_cg_u32(&t.vals[ts]), origin = v >> 26, idx = v & ((1u << 26) - 1);
+        uint32_t out = kRefKeep;
+        if (!(origin == kOriginSelf && idx == (uint32_t)gp)) {
+          const uint32_t mine = ld_cg_u32(&crc[gp]);
+          const uint32_t ocrc = origin == 0             ? crcs.parent[idx]
+                                : origin == kOriginSelf ? ld_cg_u32(&crc[idx])
+                                                        : crcs.peer[origin - 1][idx];
+          if (ocrc == mine)
+            out = origin == 0             ? (3u << 29 | idx)
+                  : origin == kOriginSelf ? (2u << 29 | idx)
+                                          : (4u << 29 | (origin - 1) << 26 | idx);
+        }
+        keep = out == kRefKeep;
+        kind = keep ? 1u : out >> 29;
+        if (!keep) ref[gp] = out;
+      }
+      if (kind < 5u) n_kind[kind]++;
+    }
+    const uint32_t bal = __ballot_sync(0xFFFFFFFFu, keep);
+    if (gw < (uint32_t)kTileWarps && lane == 0) s_warp_cnt[grp][gw] = __popc(bal);
+    group_sync(grp);
+    uint32_t before = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < kTileWarps; w++) {
+      const uint32_t c = s_warp_cnt[grp][w];
+      before += w < (int)gw ? c : 0u;
+      total += c;
+    }
+    if (gw == 0) {
+      if (lane == 0) st_status(&status[tile], (tile == 0 ? kStPrefix : kStAgg) | total);
+      uint32_t excl = 0;
+      if (tile > 0) {
+        int64_t look = (int64_t)tile - 1;
+        for (;;) {
+          const int64_t idx = look - lane;
+          unsigned long long st;
+          do {
+            st = idx >= 0 ? ld_status(&status[idx]) : kStPrefix;
+          } while (__any_sync(0xFFFFFFFFu, (st >> 62) < 2));
+          const uint32_t incl = __ballot_sync(0xFFFFFFFFu, (st >> 62) == 3);
+          const uint32_t upto = incl ? (uint32_t)__ffs(incl) - 1u : 31u;
+          uint32_t v = lane <= upto ? (uint32_t)st : 0u;
+#pragma unroll
+          for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
+          excl += v;
+          if (incl) break;
+          look -= 32;
+        }
+        if (lane == 0) st_status(&status[tile], kStPrefix | (excl + total));
+      }
+      if (lane == 0) {
+        s_excl[grp] = excl;
+        if (tile == n_tiles - 1) {
+          cnt->n_stored = excl + total;
+          cnt->slot_base_next = ref_base + excl + total;
+        }
+      }
+    }
+    const uint32_t rank = before + __popc(bal & ((1u << lane) - 1));
+    if (keep) s_list[grp][rank] = (uint16_t)gt;
+    group_sync(grp);
+    const uint64_t first_slot = out_base + s_excl[grp];
+    if (keep) {
+      ref[gp] = 1u << 29 | (uint32_t)(ref_base + s_excl[grp] + rank);
+      if (first_slot + rank >= capacity_pages) atomicAdd(&cnt->overflow, 1ull);
+    }
+
+    // ---- C: copy the stored pages (L2 hits), one page per warp per step.  The ring already
+    // holds the next tile's first loads, which leaves room for one page in flight per warp.
+    for (uint32_t k = gw; k < total; k += kGroupWarps) {
+      const uint64_t sa = first_slot + k;
+      const uint4* pa = image + (base + s_list[grp][k]) * 256 + lane;
+      uint4 va[8];
+#pragma unroll
+      for (int j = 0; j < 8; j++) va[j] = ldg_hint(pa + 32 * j, done_with);
+      if (sa < capacity_pages) {
+#pragma unroll
+        for (int j = 0; j < 8; j++) stg_hint(packed + sa * 256 + lane + 32 * j, va[j], done_with);
+      }
+    }
+    tile = next_tile;
+    // the barrier at the top of the next iteration separates these reads of s_list / s_excl / s_ts
+    // from the next tile's writes
+  }
+#pragma unroll
+  for (int k = 0; k < 5; k++) {
+    uint32_t v = n_kind[k];
+#pragma unroll
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
+    if (lane == 0 && v) atomicAdd(&cnt->kind[k], (unsigned long long)v);
+  }
+}
+
 // ------------------------------------------------------------------ K4 restore
+// Where the bytes of page p live: nullptr for a zero page or a reference that cannot be followed.
+struct PageSrc {
+  const uint4* src;
+  bool bad;
+};
+
+__device__ __forceinline__ PageSrc resolve_source(uint64_t p, bool on, const uint4* __restrict__ packed,
+                                                  uint64_t n_slots, const uint32_t* __restrict__ ref,
+                                                  uint64_t n_pages, const PeerImages& imgs) {
+  PageSrc r{nullptr, false};
+  if (!on) return r;
+  uint32_t x = ref[p], kind = x >> 29, v = x & 0x1FFFFFFFu;
+  if (kind == 2u) {  // DUP -> the owner's slot
+    const uint32_t x2 = v < n_pages ? ref[v] : 0u;
+    r.bad = (x2 >> 29) != 1u;
+    kind = 1u;
+    v = x2 & 0x1FFFFFFFu;
+  }
+  if (kind == 1u) {
+    if (!r.bad && v < n_slots) r.src = packed + (uint64_t)v * 256;
+    else r.bad = true;
+  } else if (kind == 3u) {
+    if (imgs.parent && v < imgs.parent_pages) r.src = reinterpret_cast<const uint4*>(imgs.parent) + (uint64_t)v * 256;
+    else r.bad = true;
+  } else if (kind == 4u) {
+    const uint32_t rk = v >> 26, idx = v & ((1u << 26) - 1);
+    if (rk < imgs.n_peers && imgs.peer[rk] && idx < imgs.peer_pages[rk])
+      r.src = reinterpret_cast<const uint4*>(imgs.peer[rk]) + (uint64_t)idx * 256;
+    else r.bad = true;
+  } else if (kind != 0u) {
+    r.bad = true;
+  }
+  return r;
+}
+
+// restores pages [page0, page1) of the image into out[0 .. page1-page0)
 __global__ void __launch_bounds__(kThreads, 1)
 k_restore(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ packed, uint64_t n_slots,
           const uint32_t* __restrict__ ref, const uint32_t* __restrict__ crc, uint64_t n_pages,
@@ -409,39 +740,16 @@ k_restore(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ packed, 
   const uint32_t g = lane >> 3, l = lane & 7, lane4 = lane * 4;
   const uint64_t n_groups = (page1 - page0 + 3) / 4;
   const uint64_t stride = (uint64_t)gridDim.x * kWarps;
+  uint64_t grp = (uint64_t)blockIdx.x * kWarps + warp;
+  if (grp >= n_groups) return;
 
-  // restores pages [page0, page1) of the image into out[0 .. page1-page0)
-  for (uint64_t grp = (uint64_t)blockIdx.x * kWarps + warp; grp < n_groups; grp += stride) {
+  for (; grp < n_groups; grp += stride) {
     const uint64_t p = page0 + 4 * grp + g;
     const bool on = p < page1;
-    // follow the page reference to the 4 KiB that holds its bytes
-    const uint4* src = nullptr;
-    bool bad = false;
-    if (on) {
-      uint32_t r = ref[p], kind = r >> 29, v = r & 0x1FFFFFFFu;
-      if (kind == 2u) {  // DUP -> the owner's slot
-        const uint32_t r2 = v < n_pages ? ref[v] : 0u;
-        bad = (r2 >> 29) != 1u;
-        kind = 1u;
-        v = r2 & 0x1FFFFFFFu;
-      }
-      if (kind == 1u) {
-        if (!bad && v < n_slots) src = packed + (uint64_t)v * 256;
-        else bad = true;
-      } else if (kind == 3u) {
-        if (imgs.parent && v < imgs.parent_pages) src = reinterpret_cast<const uint4*>(imgs.parent) + (uint64_t)v * 256;
-        else bad = true;
-      } else if (kind == 4u) {
-        const uint32_t rk = v >> 26, idx = v & ((1u << 26) - 1);
-        if (rk < imgs.n_peers && imgs.peer[rk] && idx < imgs.peer_pages[rk])
-          src = reinterpret_cast<const uint4*>(imgs.peer[rk]) + (uint64_t)idx * 256;
-        else bad = true;
-      } else if (kind != 0u) {
-        bad = true;
-      }
-    }
-    const bool have = src != nullptr;
-    const uint4* s = have ? src + l : packed;  // never dereferenced when !have
+    const PageSrc ps = resolve_source(p, on, packed, n_slots, ref, n_pages, imgs);
+    const bool have = ps.src != nullptr;
+    bool bad = ps.bad;
+    const uint4* s = have ? ps.src + l : packed;  // never dereferenced without a source
     uint4* d = out + (p - page0) * 256 + l;
     PageAcc a;
     a.z = 0;
@@ -518,7 +826,24 @@ uint32_t page_kernel_smem_bytes() { return kSmBytes; }
 cudaError_t configure_kernels() {
   cudaError_t e = cudaFuncSetAttribute(k_analyze, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmBytes);
   if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(k_pack_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmBytes);
+  if (e != cudaSuccess) return e;
   return cudaFuncSetAttribute(k_restore, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmBytes);
+}
+
+uint32_t fused_tile_pages() { return kFusedTile; }
+
+cudaError_t launch_pack_fused(const LaunchGeom& g, const Gf2Tables* d_tab, const void* d_image, uint64_t n_pages,
+                              uint64_t page0, uint32_t* d_crc, uint64_t* d_hash, uint32_t* d_ref, DedupTable t,
+                              PeerCrcs crcs, void* d_packed, uint64_t capacity_pages, uint64_t slot_base, bool chained,
+                              unsigned long long* d_tile_status, DevCounters* d_cnt, cudaStream_t s) {
+  if (!n_pages) return cudaSuccess;
+  const int grid = grid_for(g, n_pages, kFusedTile * kGroups, 1);
+  k_pack_fused<<<grid, kThreads, kSmBytes, s>>>(d_tab, static_cast<const uint4*>(d_image), n_pages, page0, d_crc,
+                                                reinterpret_cast<unsigned long long*>(d_hash), d_ref, t, crcs,
+                                                static_cast<uint4*>(d_packed), capacity_pages, slot_base,
+                                                chained ? 1 : 0, d_tile_status, d_cnt);
+  return cudaGetLastError();
 }
 
 cudaError_t launch_analyze(const LaunchGeom& g, const Gf2Tables* d_tab, const void* d_image, uint64_t n_pages,

@@ -63,6 +63,12 @@ cudaError_t launch_resolve(const LaunchGeom& g, DedupTable t, uint64_t page0, ui
 cudaError_t launch_compact(const LaunchGeom& g, const void* d_image, uint64_t n_pages, uint32_t* d_ref,
                            void* d_packed, uint64_t capacity_pages, uint64_t slot_base, bool chained,
                            unsigned long long* d_tile_status, DevCounters* d_cnt, cudaStream_t s);
+// K1+K2+K3 in one pass; crc/hash/ref are the whole image's arrays, the chunk starts at page0 of them
+cudaError_t launch_pack_fused(const LaunchGeom& g, const Gf2Tables* d_tab, const void* d_image, uint64_t n_pages,
+                              uint64_t page0, uint32_t* d_crc, uint64_t* d_hash, uint32_t* d_ref, DedupTable t,
+                              PeerCrcs crcs, void* d_packed, uint64_t capacity_pages, uint64_t slot_base, bool chained,
+                              unsigned long long* d_tile_status, DevCounters* d_cnt, cudaStream_t s);
+uint32_t fused_tile_pages();
 cudaError_t launch_restore(const LaunchGeom& g, const Gf2Tables* d_tab, const void* d_packed,
                            uint64_t n_slots, const uint32_t* d_ref, const uint32_t* d_crc,
                            uint64_t n_pages, uint64_t page0, uint64_t page1, PeerImages imgs, void* d_out,
