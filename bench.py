@@ -226,14 +226,10 @@ def run_gritpack(args):
         """K1 -> [hash all-gather over NCCL when world > 1] -> K2 -> K3."""
         if world == 1:
             return ctx.pack(image, packed=packed, out=meta)
-        ref, crc, h = meta
-        crc2, h2, ref2 = ctx.analyze(image)
-        crc.copy_(crc2), h.copy_(h2), ref.copy_(ref2)
-        hs = [torch.empty_like(h) for _ in range(world)]
-        cs = [torch.empty_like(crc) for _ in range(world)]
-        dist.all_gather(hs, h)
-        dist.all_gather(cs, crc)
-        ctx.dedup(crc, h, ref, peers=[(hs[q], cs[q]) for q in range(rank)])
+        from grit_b200 import dist as gdist
+        crc, h, ref = ctx.analyze(image)
+        tables = gdist.all_gather_tables(h, crc)          # NCCL over NVLink: 12 B per 4 KiB page
+        ctx.dedup(crc, h, ref, peers=gdist.peers_of(rank, tables))
         n = ctx.compact(image, ref, packed)
         return dict(ref=ref, crc=crc, hash=h, packed=packed[: n * PAGE], stats={"n_data": n})
 
@@ -312,11 +308,39 @@ def run_gritpack(args):
         s["frac"] = s["gbs"] / peak if s["gbs"] else None
         s["ms"] = round(s["ms"], 4)
     dom = max(stages, key=lambda k: stages[k]["ms"])
+    traffic, traffic_src = None, None
+    try:  # dram__bytes_read + write of one launch at this size, from the committed ncu --set full capture
+        tr = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        if tr.get("pages") == n_pages and dom in tr["kernels"]:
+            traffic, traffic_src = tr["kernels"][dom]["dram_bytes"], tr["source"]
+    except Exception:
+        pass
     roofline = {"bound": "hbm", "kernel": dom, "achieved": round(stages[dom]["gbs"], 1), "peak": peak,
-                "peak_source": peak_src, "unit": "GB/s", "frac": round(stages[dom]["frac"], 4), "traffic": None,
-                "stages": stages,
+                "peak_source": peak_src, "unit": "GB/s", "frac": round(stages[dom]["frac"], 4), "traffic": traffic,
+                "traffic_source": traffic_src, "alg_bytes": stages[dom]["alg_bytes"], "stages": stages,
                 "pack_whole": {"ms": round(t_pack, 4), "alg_bytes": n_bytes + U + 16 * n_pages,
                                "frac": round((n_bytes + U + 16 * n_pages) / (t_pack * 1e-3) / 1e9 / peak, 4)}}
+
+    # ---- host link peaks of this box, measured now: the binding roofline of the e2e number
+    def link_peaks(h_a, h_b, d_a, d_b):
+        s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+        n = min(h_a.numel(), 1 << 30)
+        res = {}
+        for mode in ("h2d", "d2h", "both"):
+            for reps in (1, 4):
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                for _ in range(reps):
+                    if mode != "d2h":
+                        with torch.cuda.stream(s1):
+                            d_a[:n].copy_(h_a[:n], non_blocking=True)
+                    if mode != "h2d":
+                        with torch.cuda.stream(s2):
+                            h_b[:n].copy_(d_b[:n], non_blocking=True)
+                torch.cuda.synchronize()
+                res[mode] = round(reps * n / (time.perf_counter() - t0) / 1e9, 2)
+        return {"h2d_gbs": res["h2d"], "d2h_gbs": res["d2h"], "both_gbs_per_direction": res["both"],
+                "how": "pinned cudaMemcpyAsync, 1 GiB x 4, same process"}
 
     # ---- e2e: pinned host buffers through grit_pack_host / grit_restore_host
     e2e = None
@@ -331,11 +355,12 @@ def run_gritpack(args):
         h_img.copy_(image[:hb])
         h_packed = torch.empty(hb, dtype=torch.uint8, pin_memory=True)
         h_out = torch.empty(hb, dtype=torch.uint8, pin_memory=True)
-        k_e2e = max(1, min(args.steps, 3))
-        for _ in range(1):
+        k_e2e = max(1, min(args.steps, 5))
+        for _ in range(2):
             hr = ctx.pack_host(h_img, packed=h_packed)
             ctx.restore_host(hr["packed"], hr["ref"], hr["crc"], out=h_out)
         assert torch.equal(h_out, h_img), "e2e restored image differs"
+        link = link_peaks(h_img, h_out, packed, restored)
         barrier()
         t0 = time.perf_counter()
         for _ in range(k_e2e):
@@ -349,7 +374,10 @@ def run_gritpack(args):
         hu = int(hr["stats"]["n_data"]) * PAGE
         e2e = {"value": round(world * 2 * hb / (float(dt.item()) / k_e2e) / 1e9, 3), "unit": "GB/s",
                "h2d_bytes_per_step": hb + hu + 8 * e2e_pages, "d2h_bytes_per_step": hu + hb + 16 * e2e_pages,
-               "steps": k_e2e, "image_bytes": hb,
+               "steps": k_e2e, "image_bytes": hb, "link": link,
+               "frac_of_link": round(2 * hb / (float(dt.item()) / k_e2e) / 1e9 / link["both_gbs_per_direction"], 3),
+               "bound": "PCIe Gen5 x16, both directions busy: each direction carries the image once per pack and "
+                        "once per restore",
                "api": "grit_pack_host + grit_restore_host (pinned host buffers, 64 MiB chunks, 3 streams)"}
         del h_img, h_packed, h_out
 

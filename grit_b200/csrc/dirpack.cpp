@@ -520,6 +520,7 @@ int grit_pack_dir(const char* src_dir, const char* dst_dir, const grit_opts* opt
   grit_pack_stats ps{};
   {
     PackStream pk(ctx, m.n_pages, o.chunk_pages);
+    pk.set_outputs(ref.data(), crc.data(), hash.data());
     if (int rc = pk.begin(parent.n_pages ? &parent : nullptr, err, errlen)) return rc;
     if (m.n_pages)
       if (int rc = pk.alloc_staging(true, true, err, errlen)) return rc;
@@ -610,7 +611,7 @@ int grit_pack_dir(const char* src_dir, const char* dst_dir, const grit_opts* opt
     stop_writer();
     if (!rc && !werr.empty()) rc = fail(err, errlen, GRIT_EIO, "%s", werr.c_str());
     if (rc) return rc;
-    if ((rc = pk.finish(ref.data(), crc.data(), hash.data(), &ps, err, errlen))) return rc;
+    if ((rc = pk.finish(&ps, err, errlen))) return rc;
     st.h2d_bytes = pk.h2d_bytes;
     st.d2h_bytes = pk.d2h_bytes;
   }

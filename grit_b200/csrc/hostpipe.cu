@@ -3,10 +3,28 @@
 #include "hostpipe.h"
 
 #include <algorithm>
+#include <chrono>
 #include <cstdlib>
 #include <cstring>
 
 using namespace grit;
+
+namespace {
+// pipeline chunk of the host-buffer entry points: 64 MiB unless GRITPACK_CHUNK_MB says otherwise
+uint64_t host_chunk_pages() {
+  static const uint64_t v = [] {
+    const char* e = getenv("GRITPACK_CHUNK_MB");
+    const uint64_t mb = e ? strtoull(e, nullptr, 10) : 0;
+    return ((mb >= 1 && mb <= 4096 ? mb : 64) << 20) / kPage;
+  }();
+  return v;
+}
+double wall() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+bool debug_on() {
+  static const bool v = getenv("GRITPACK_DEBUG") != nullptr;
+  return v;
+}
+}  // namespace
 
 namespace grit {
 
@@ -38,6 +56,8 @@ PackStream::~PackStream() {
     if (ev_d2h_[b]) cudaEventDestroy(ev_d2h_[b]);
   }
   if (h_counts_) cudaFreeHost(h_counts_);
+  for (int b = 0; b < kPipeDepth; b++)
+    if (h_meta_[b]) cudaFreeHost(h_meta_[b]);
   if (d_ref_) cudaFree(d_ref_);
   if (d_crc_) cudaFree(d_crc_);
   if (d_hash_) cudaFree(d_hash_);
@@ -57,6 +77,7 @@ int PackStream::begin(const grit_table* parent, char* err, size_t errlen) {
     GRIT_CUDA(cudaEventCreateWithFlags(&ev_d2h_[b], cudaEventDisableTiming));
   }
   GRIT_CUDA(cudaMallocHost(&h_counts_, kPipeDepth * sizeof(unsigned long long)));
+  for (int b = 0; b < kPipeDepth; b++) GRIT_CUDA(cudaMallocHost(&h_meta_[b], chunk_pages_ * 16));
   const uint64_t n = std::max<uint64_t>(total_pages_, 1);
   GRIT_CUDA(cudaMalloc(&d_ref_, n * 4));
   GRIT_CUDA(cudaMalloc(&d_crc_, n * 4));
@@ -134,6 +155,13 @@ int PackStream::submit(uint64_t i, const void* h_src, uint64_t n_pages, char* er
     ctx_->launches++;
   }
   GRIT_CUDA(cudaMemcpyAsync(&h_counts_[b], &ctx_->d_cnt->n_stored, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+  // the chunk's per-page arrays are final now: bring them to pinned staging (u32 ref | u32 crc | u64 hash)
+  char* meta = static_cast<char*>(h_meta_[b]);
+  GRIT_CUDA(cudaMemcpyAsync(meta, d_ref_ + p0, n_pages * 4, cudaMemcpyDeviceToHost, s));
+  GRIT_CUDA(cudaMemcpyAsync(meta + chunk_pages_ * 4, d_crc_ + p0, n_pages * 4, cudaMemcpyDeviceToHost, s));
+  GRIT_CUDA(cudaMemcpyAsync(meta + chunk_pages_ * 8, d_hash_ + p0, n_pages * 8, cudaMemcpyDeviceToHost, s));
+  chunk_pages_n_[b] = n_pages;
+  d2h_bytes += n_pages * 16.0;
   // the next launch continues the slot numbering from here
   GRIT_CUDA(cudaMemcpyAsync(&ctx_->d_cnt->slot_base, &ctx_->d_cnt->slot_base_next, sizeof(unsigned long long),
                             cudaMemcpyDeviceToDevice, s));
@@ -146,6 +174,13 @@ int PackStream::collect(uint64_t i, void* h_dst, uint64_t* first_slot, uint64_t*
   const int b = (int)(i % kPipeDepth);
   GRIT_CUDA(cudaEventSynchronize(ev_kern_[b]));
   const uint64_t n = h_counts_[b];
+  {
+    const char* meta = static_cast<const char*>(h_meta_[b]);
+    const uint64_t p0 = chunk_page0_[b], np = chunk_pages_n_[b];
+    if (out_ref_) memcpy(out_ref_ + p0, meta, np * 4);
+    if (out_crc_) memcpy(out_crc_ + p0, meta + chunk_pages_ * 4, np * 4);
+    if (out_hash_) memcpy(out_hash_ + p0, meta + chunk_pages_ * 8, np * 8);
+  }
   *first_slot = slots_done_;
   *n_out = n;
   GRIT_CUDA(cudaStreamWaitEvent(ctx_->d2h, ev_kern_[b], 0));
@@ -171,16 +206,9 @@ int PackStream::wait_out(uint64_t i, char* err, size_t errlen) {
   return GRIT_OK;
 }
 
-int PackStream::finish(uint32_t* h_ref, uint32_t* h_crc, uint64_t* h_hash, grit_pack_stats* stats, char* err,
-                       size_t errlen) {
+int PackStream::finish(grit_pack_stats* stats, char* err, size_t errlen) {
   cudaStream_t s = ctx_->stream;
   if (timing_started_) GRIT_CUDA(cudaEventRecord(ctx_->ev1, s));
-  if (total_pages_) {
-    if (h_ref) GRIT_CUDA(cudaMemcpyAsync(h_ref, d_ref_, total_pages_ * 4, cudaMemcpyDeviceToHost, s));
-    if (h_crc) GRIT_CUDA(cudaMemcpyAsync(h_crc, d_crc_, total_pages_ * 4, cudaMemcpyDeviceToHost, s));
-    if (h_hash) GRIT_CUDA(cudaMemcpyAsync(h_hash, d_hash_, total_pages_ * 8, cudaMemcpyDeviceToHost, s));
-    d2h_bytes += total_pages_ * 16.0;
-  }
   if (int rc = read_counters(ctx_, s, err, errlen)) return rc;
   GRIT_CUDA(cudaStreamSynchronize(ctx_->d2h));
   GRIT_CUDA(cudaStreamSynchronize(ctx_->h2d));
@@ -249,6 +277,7 @@ int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const u
 
   cudaStream_t s = ctx->stream;
   const size_t chunk_bytes = chunk_pages * kPage;
+  const double t_begin = wall();
   GRIT_CUDA(cudaMalloc(&r.d_packed, std::max<uint64_t>(n_slots, 1) * kPage));
   GRIT_CUDA(cudaMalloc(&r.d_ref, std::max<uint64_t>(n_pages, 1) * 4));
   GRIT_CUDA(cudaMalloc(&r.d_crc, std::max<uint64_t>(n_pages, 1) * 4));
@@ -310,6 +339,7 @@ int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const u
   };
 
   GRIT_CUDA(cudaEventRecord(ctx->ev0, s));
+  const double t_loop = wall();
   uint64_t slot_front = 0;  // slots referenced by pages before the current chunk end
   for (uint64_t i = 0; i < n_chunks + 1; i++) {
     if (i < n_chunks) {
@@ -353,6 +383,9 @@ int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const u
   }
   if (h2d_total) *h2d_total += h2d;
   if (d2h_total) *d2h_total += d2h;
+  if (debug_on())
+    fprintf(stderr, "[gritpack] restore_stream: alloc %.1f ms, stream %.1f ms\n", (t_loop - t_begin) * 1e3,
+            (wall() - t_loop) * 1e3);
   const DevCounters& c = *ctx->h_cnt;
   if (stats) {
     stats->n_pages = n_pages;
@@ -385,11 +418,14 @@ int grit_pack_host(grit_ctx* ctx, const void* h_image, uint64_t n_pages, const g
     return fail(err, errlen, GRIT_EINVAL, "null buffer");
   std::lock_guard<std::mutex> g(ctx->mu);
   GRIT_CUDA(cudaSetDevice(ctx->device));
-  const uint64_t chunk_pages = (64ull << 20) / kPage;
+  const uint64_t chunk_pages = host_chunk_pages();
   const uint64_t n_chunks = (n_pages + chunk_pages - 1) / chunk_pages;
   const bool in_pinned = is_pinned(h_image), out_pinned = is_pinned(h_packed);
+  const double t_begin = wall();
   PackStream ps(ctx, n_pages, chunk_pages);
+  ps.set_outputs(h_ref, h_crc, h_hash);
   if (int rc = ps.begin(parent, err, errlen)) return rc;
+  const double t_loop = wall();
   // pageable caller memory is bounced through pinned staging (one memcpy each way)
   if (n_pages)
     if (int rc = ps.alloc_staging(!in_pinned, !out_pinned, err, errlen)) return rc;
@@ -437,7 +473,12 @@ int grit_pack_host(grit_ctx* ctx, const void* h_image, uint64_t n_pages, const g
     for (uint64_t i = first; i < n_chunks; i++)
       if (int rc = drain(i)) return rc;
   }
-  return ps.finish(h_ref, h_crc, h_hash, stats, err, errlen);
+  const double t_fin = wall();
+  const int rc = ps.finish(stats, err, errlen);
+  if (debug_on())
+    fprintf(stderr, "[gritpack] pack_host: begin %.1f ms, stream %.1f ms, finish %.1f ms\n", (t_loop - t_begin) * 1e3,
+            (t_fin - t_loop) * 1e3, (wall() - t_fin) * 1e3);
+  return rc;
 }
 
 int grit_restore_host(grit_ctx* ctx, const void* h_packed, uint64_t n_slots, const uint32_t* h_ref,
@@ -465,7 +506,7 @@ int grit_restore_host(grit_ctx* ctx, const void* h_packed, uint64_t n_slots, con
     };
   }
   return restore_stream(ctx, io, n_slots, h_ref, h_crc, n_pages, h_parent_image, parent_pages, false, verify,
-                        (64ull << 20) / kPage, stats, nullptr, nullptr, err, errlen);
+                        host_chunk_pages(), stats, nullptr, nullptr, err, errlen);
 }
 
 }  // extern "C"

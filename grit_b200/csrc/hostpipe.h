@@ -42,8 +42,14 @@ class PackStream {
                  char* err, size_t errlen);
   // blocks until chunk i's D2H has landed
   int wait_out(uint64_t i, char* err, size_t errlen);
-  // download the per-page arrays and the statistics; syncs everything
-  int finish(uint32_t* h_ref, uint32_t* h_crc, uint64_t* h_hash, grit_pack_stats* stats, char* err, size_t errlen);
+  // host arrays (any memory) that collect() fills with each chunk's ref / crc / hash
+  void set_outputs(uint32_t* h_ref, uint32_t* h_crc, uint64_t* h_hash) {
+    out_ref_ = h_ref;
+    out_crc_ = h_crc;
+    out_hash_ = h_hash;
+  }
+  // statistics; syncs everything.  Every chunk must have been collected.
+  int finish(grit_pack_stats* stats, char* err, size_t errlen);
   uint64_t chunk_pages() const { return chunk_pages_; }
   double h2d_bytes = 0, d2h_bytes = 0;
 
@@ -56,6 +62,10 @@ class PackStream {
   void* h_out_[kPipeDepth] = {};
   cudaEvent_t ev_h2d_[kPipeDepth] = {}, ev_kern_[kPipeDepth] = {}, ev_d2h_[kPipeDepth] = {};
   unsigned long long* h_counts_ = nullptr;  // pinned: n_stored per in-flight chunk
+  void* h_meta_[kPipeDepth] = {};           // pinned: ref | crc | hash of the in-flight chunks
+  uint64_t chunk_pages_n_[kPipeDepth] = {};
+  uint32_t *out_ref_ = nullptr, *out_crc_ = nullptr;
+  uint64_t* out_hash_ = nullptr;
   uint32_t *d_ref_ = nullptr, *d_crc_ = nullptr;
   uint64_t* d_hash_ = nullptr;
   uint64_t* d_parent_hash_ = nullptr;

@@ -1,0 +1,42 @@
+"""Cross-rank exchange of the per-page hash tables.
+
+The pack path shards by image: rank r packs its own image on its own GPU.  The one exchange step is an
+all-gather of every rank's (hash64, crc32c) arrays -- 12 bytes per 4 KiB page, 0.3 % of the image -- after K1, so
+that K2 can turn pages a lower rank already stores into PEER references.  torch.distributed does the plumbing
+(NCCL over NVLink on GPUs; gloo in the CPU tests); the reference has no counterpart (one agent Job per pod,
+no cross-pod step: docs/proposals/20250221-gpu-workload-checkpointing-and-restoration.md:63-65).
+"""
+import torch
+import torch.distributed as dist
+
+
+def all_gather_tables(h, crc, group=None):
+    """h: int64[n_pages], crc: int32[n_pages] of this rank (any device the backend supports).
+
+    Ranks may hold different page counts: counts are gathered first and the arrays padded to the maximum.
+    Returns [(hash_r, crc_r) for r in range(world)], each trimmed to rank r's own page count.
+    """
+    world = dist.get_world_size(group)
+    n = torch.tensor([h.numel()], dtype=torch.int64, device=h.device)
+    counts = [torch.zeros_like(n) for _ in range(world)]
+    dist.all_gather(counts, n, group=group)
+    counts = [int(c.item()) for c in counts]
+    m = max(counts + [1])
+
+    def padded(t):
+        if t.numel() == m:
+            return t.contiguous()
+        out = torch.zeros(m, dtype=t.dtype, device=t.device)
+        out[: t.numel()] = t
+        return out
+
+    hs = [torch.empty(m, dtype=h.dtype, device=h.device) for _ in range(world)]
+    cs = [torch.empty(m, dtype=crc.dtype, device=crc.device) for _ in range(world)]
+    dist.all_gather(hs, padded(h), group=group)
+    dist.all_gather(cs, padded(crc), group=group)
+    return [(hs[r][: counts[r]], cs[r][: counts[r]]) for r in range(world)]
+
+
+def peers_of(rank, tables):
+    """The tables a rank may refer to: those of the ranks below it, in rank order (lowest rank owns a page)."""
+    return list(tables[:rank])
