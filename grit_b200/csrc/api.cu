@@ -57,6 +57,32 @@ int read_counters(grit_ctx* ctx, cudaStream_t s, char* err, size_t errlen) {
 // The pack runs K1, K2, K3 as three kernels (DRAM traffic N + 2U).  GRITPACK_FUSED=1 selects the
 // experimental single-pass kernel (k_pack_fused, N + U when its re-reads hit L2); on B200 it is
 // currently slower, so it is opt-in.
+int ctx_dev(grit_ctx* ctx, int id, size_t bytes, void** out, char* err, size_t errlen) {
+  grit_ctx::Buf& b = ctx->dev[id];
+  if (bytes > b.cap) {
+    if (b.p) cudaFree(b.p);
+    b.p = nullptr;
+    b.cap = 0;
+    GRIT_CUDA(cudaMalloc(&b.p, bytes));
+    b.cap = bytes;
+  }
+  *out = b.p;
+  return GRIT_OK;
+}
+
+int ctx_pin(grit_ctx* ctx, int id, size_t bytes, void** out, char* err, size_t errlen) {
+  grit_ctx::Buf& b = ctx->pin[id];
+  if (bytes > b.cap) {
+    if (b.p) cudaFreeHost(b.p);
+    b.p = nullptr;
+    b.cap = 0;
+    GRIT_CUDA(cudaMallocHost(&b.p, bytes));
+    b.cap = bytes;
+  }
+  *out = b.p;
+  return GRIT_OK;
+}
+
 bool staged_pack() {
   static const bool v = [] {
     const char* e = getenv("GRITPACK_FUSED");
@@ -196,7 +222,11 @@ int grit_ctx_create(int device, grit_ctx** out, char* err, size_t errlen) {
 void grit_ctx_destroy(grit_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
-  if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  cudaDeviceSynchronize();
+  for (auto& b : ctx->dev)
+    if (b.p) cudaFree(b.p);
+  for (auto& b : ctx->pin)
+    if (b.p) cudaFreeHost(b.p);
   if (ctx->d_keys) cudaFree(ctx->d_keys);
   if (ctx->d_vals) cudaFree(ctx->d_vals);
   if (ctx->d_status) cudaFree(ctx->d_status);

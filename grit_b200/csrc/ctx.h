@@ -28,6 +28,13 @@ struct grit_ctx {
   uint64_t status_cap = 0;
   uint64_t launches = 0;
   std::mutex mu;
+  // Working buffers of the host pipelines, kept between calls (grown on demand, freed with the
+  // context) so that a steady stream of packs/restores does no cudaMalloc/cudaFree at all.
+  struct Buf {
+    void* p = nullptr;
+    size_t cap = 0;
+  };
+  Buf dev[24], pin[16];
 };
 
 namespace grit {
@@ -55,6 +62,12 @@ int ensure_table(grit_ctx* ctx, uint64_t n_items, DedupTable* t, char* err, size
 int ensure_status(grit_ctx* ctx, uint64_t n_pages, char* err, size_t errlen);
 int reset_counters(grit_ctx* ctx, cudaStream_t s, char* err, size_t errlen);
 int read_counters(grit_ctx* ctx, cudaStream_t s, char* err, size_t errlen);  // syncs s
+// cached device / pinned-host buffer number `id` of at least `bytes` bytes (contents undefined)
+int ctx_dev(grit_ctx* ctx, int id, size_t bytes, void** out, char* err, size_t errlen);
+int ctx_pin(grit_ctx* ctx, int id, size_t bytes, void** out, char* err, size_t errlen);
+enum DevBuf { kDevIn0 = 0, kDevOut0 = 3, kDevRef = 6, kDevCrc, kDevHash, kDevParentHash, kDevParentCrc,
+              kDevRPacked, kDevRRef, kDevRCrc, kDevROut0 = 14, kDevRParent = 17 };
+enum PinBuf { kPinIn0 = 0, kPinOut0 = 3, kPinCounts = 6, kPinMeta0 = 7, kPinRStageOut0 = 10, kPinRStageIn0 = 13 };
 bool staged_pack();  // true unless GRITPACK_FUSED=1 selects the experimental single-pass pack kernel
 
 }  // namespace grit

@@ -47,22 +47,11 @@ PackStream::~PackStream() {
   cudaStreamSynchronize(ctx_->stream);
   cudaStreamSynchronize(ctx_->d2h);
   for (int b = 0; b < kPipeDepth; b++) {
-    if (d_in_[b]) cudaFree(d_in_[b]);
-    if (d_out_[b]) cudaFree(d_out_[b]);
-    if (h_in_[b]) cudaFreeHost(h_in_[b]);
-    if (h_out_[b]) cudaFreeHost(h_out_[b]);
     if (ev_h2d_[b]) cudaEventDestroy(ev_h2d_[b]);
     if (ev_kern_[b]) cudaEventDestroy(ev_kern_[b]);
     if (ev_d2h_[b]) cudaEventDestroy(ev_d2h_[b]);
   }
-  if (h_counts_) cudaFreeHost(h_counts_);
-  for (int b = 0; b < kPipeDepth; b++)
-    if (h_meta_[b]) cudaFreeHost(h_meta_[b]);
-  if (d_ref_) cudaFree(d_ref_);
-  if (d_crc_) cudaFree(d_crc_);
-  if (d_hash_) cudaFree(d_hash_);
-  if (d_parent_hash_) cudaFree(d_parent_hash_);
-  if (d_parent_crc_) cudaFree(d_parent_crc_);
+  // the buffers belong to the context's cache and stay for the next call
 }
 
 int PackStream::begin(const grit_table* parent, char* err, size_t errlen) {
@@ -70,24 +59,25 @@ int PackStream::begin(const grit_table* parent, char* err, size_t errlen) {
   if (total_pages_ > GRIT_MAX_PAGES) return fail(err, errlen, GRIT_EINVAL, "image exceeds GRIT_MAX_PAGES");
   const size_t chunk_bytes = chunk_pages_ * kPage;
   for (int b = 0; b < kPipeDepth; b++) {
-    GRIT_CUDA(cudaMalloc(&d_in_[b], chunk_bytes));
-    GRIT_CUDA(cudaMalloc(&d_out_[b], chunk_bytes));
+    if (int rc = ctx_dev(ctx_, kDevIn0 + b, chunk_bytes, &d_in_[b], err, errlen)) return rc;
+    if (int rc = ctx_dev(ctx_, kDevOut0 + b, chunk_bytes, &d_out_[b], err, errlen)) return rc;
     GRIT_CUDA(cudaEventCreateWithFlags(&ev_h2d_[b], cudaEventDisableTiming));
     GRIT_CUDA(cudaEventCreateWithFlags(&ev_kern_[b], cudaEventDisableTiming));
     GRIT_CUDA(cudaEventCreateWithFlags(&ev_d2h_[b], cudaEventDisableTiming));
   }
-  GRIT_CUDA(cudaMallocHost(&h_counts_, kPipeDepth * sizeof(unsigned long long)));
-  for (int b = 0; b < kPipeDepth; b++) GRIT_CUDA(cudaMallocHost(&h_meta_[b], chunk_pages_ * 16));
+  if (int rc = ctx_pin(ctx_, kPinCounts, kPipeDepth * sizeof(unsigned long long), (void**)&h_counts_, err, errlen)) return rc;
+  for (int b = 0; b < kPipeDepth; b++)
+    if (int rc = ctx_pin(ctx_, kPinMeta0 + b, chunk_pages_ * 16, &h_meta_[b], err, errlen)) return rc;
   const uint64_t n = std::max<uint64_t>(total_pages_, 1);
-  GRIT_CUDA(cudaMalloc(&d_ref_, n * 4));
-  GRIT_CUDA(cudaMalloc(&d_crc_, n * 4));
-  GRIT_CUDA(cudaMalloc(&d_hash_, n * 8));
+  if (int rc = ctx_dev(ctx_, kDevRef, n * 4, (void**)&d_ref_, err, errlen)) return rc;
+  if (int rc = ctx_dev(ctx_, kDevCrc, n * 4, (void**)&d_crc_, err, errlen)) return rc;
+  if (int rc = ctx_dev(ctx_, kDevHash, n * 8, (void**)&d_hash_, err, errlen)) return rc;
   uint64_t items = total_pages_;
   if (parent && parent->n_pages) {
     if (parent->n_pages > GRIT_MAX_PAGES) return fail(err, errlen, GRIT_EINVAL, "parent exceeds GRIT_MAX_PAGES");
     items += parent->n_pages;
-    GRIT_CUDA(cudaMalloc(&d_parent_hash_, parent->n_pages * 8));
-    GRIT_CUDA(cudaMalloc(&d_parent_crc_, parent->n_pages * 4));
+    if (int rc = ctx_dev(ctx_, kDevParentHash, parent->n_pages * 8, (void**)&d_parent_hash_, err, errlen)) return rc;
+    if (int rc = ctx_dev(ctx_, kDevParentCrc, parent->n_pages * 4, (void**)&d_parent_crc_, err, errlen)) return rc;
     GRIT_CUDA(cudaMemcpyAsync(d_parent_hash_, parent->hash, parent->n_pages * 8, cudaMemcpyHostToDevice, ctx_->stream));
     GRIT_CUDA(cudaMemcpyAsync(d_parent_crc_, parent->crc, parent->n_pages * 4, cudaMemcpyHostToDevice, ctx_->stream));
     crcs_.parent = d_parent_crc_;
@@ -108,8 +98,10 @@ int PackStream::begin(const grit_table* parent, char* err, size_t errlen) {
 
 int PackStream::alloc_staging(bool in, bool out, char* err, size_t errlen) {
   for (int b = 0; b < kPipeDepth; b++) {
-    if (in && !h_in_[b]) GRIT_CUDA(cudaMallocHost(&h_in_[b], chunk_pages_ * kPage));
-    if (out && !h_out_[b]) GRIT_CUDA(cudaMallocHost(&h_out_[b], chunk_pages_ * kPage));
+    if (in && !h_in_[b])
+      if (int rc = ctx_pin(ctx_, kPinIn0 + b, chunk_pages_ * kPage, &h_in_[b], err, errlen)) return rc;
+    if (out && !h_out_[b])
+      if (int rc = ctx_pin(ctx_, kPinOut0 + b, chunk_pages_ * kPage, &h_out_[b], err, errlen)) return rc;
   }
   return GRIT_OK;
 }
@@ -249,28 +241,19 @@ int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const u
 
   struct Res {
     void *d_packed = nullptr, *d_parent = nullptr, *d_out[kPipeDepth] = {}, *h_stage_out[kPipeDepth] = {};
-    bool own_parent = false;
     void* h_stage_in[2] = {};
     uint32_t *d_ref = nullptr, *d_crc = nullptr;
     cudaEvent_t ev_kern[kPipeDepth] = {}, ev_d2h[kPipeDepth] = {};
     std::vector<cudaEvent_t> ev_up;
     cudaEvent_t ev_stage[2] = {};
     ~Res() {
-      cudaDeviceSynchronize();
-      cudaFree(d_packed);
-      if (own_parent) cudaFree(d_parent);
-      cudaFree(d_ref);
-      cudaFree(d_crc);
+      cudaDeviceSynchronize();  // nothing of this call may still be running when the cached buffers are reused
       for (int b = 0; b < kPipeDepth; b++) {
-        cudaFree(d_out[b]);
-        if (h_stage_out[b]) cudaFreeHost(h_stage_out[b]);
         if (ev_kern[b]) cudaEventDestroy(ev_kern[b]);
         if (ev_d2h[b]) cudaEventDestroy(ev_d2h[b]);
       }
-      for (int b = 0; b < 2; b++) {
-        if (h_stage_in[b]) cudaFreeHost(h_stage_in[b]);
+      for (int b = 0; b < 2; b++)
         if (ev_stage[b]) cudaEventDestroy(ev_stage[b]);
-      }
       for (auto e : ev_up) cudaEventDestroy(e);
     }
   } r;
@@ -278,14 +261,15 @@ int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const u
   cudaStream_t s = ctx->stream;
   const size_t chunk_bytes = chunk_pages * kPage;
   const double t_begin = wall();
-  GRIT_CUDA(cudaMalloc(&r.d_packed, std::max<uint64_t>(n_slots, 1) * kPage));
-  GRIT_CUDA(cudaMalloc(&r.d_ref, std::max<uint64_t>(n_pages, 1) * 4));
-  GRIT_CUDA(cudaMalloc(&r.d_crc, std::max<uint64_t>(n_pages, 1) * 4));
+  if (int rc = ctx_dev(ctx, kDevRPacked, std::max<uint64_t>(n_slots, 1) * kPage, &r.d_packed, err, errlen)) return rc;
+  if (int rc = ctx_dev(ctx, kDevRRef, std::max<uint64_t>(n_pages, 1) * 4, (void**)&r.d_ref, err, errlen)) return rc;
+  if (int rc = ctx_dev(ctx, kDevRCrc, std::max<uint64_t>(n_pages, 1) * 4, (void**)&r.d_crc, err, errlen)) return rc;
   for (int b = 0; b < kPipeDepth; b++) {
-    GRIT_CUDA(cudaMalloc(&r.d_out[b], chunk_bytes));
+    if (int rc = ctx_dev(ctx, kDevROut0 + b, chunk_bytes, &r.d_out[b], err, errlen)) return rc;
     GRIT_CUDA(cudaEventCreateWithFlags(&r.ev_kern[b], cudaEventDisableTiming));
     GRIT_CUDA(cudaEventCreateWithFlags(&r.ev_d2h[b], cudaEventDisableTiming));
-    if (!out_pinned) GRIT_CUDA(cudaMallocHost(&r.h_stage_out[b], chunk_bytes));
+    if (!out_pinned)
+      if (int rc = ctx_pin(ctx, kPinRStageOut0 + b, chunk_bytes, &r.h_stage_out[b], err, errlen)) return rc;
   }
   double h2d = 0, d2h = 0;
   if (n_pages) {
@@ -298,8 +282,7 @@ int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const u
     if (parent_on_device) {
       r.d_parent = const_cast<void*>(parent_image);
     } else {
-      GRIT_CUDA(cudaMalloc(&r.d_parent, parent_pages * kPage));
-      r.own_parent = true;
+      if (int rc = ctx_dev(ctx, kDevRParent, parent_pages * kPage, &r.d_parent, err, errlen)) return rc;
       GRIT_CUDA(cudaMemcpyAsync(r.d_parent, parent_image, parent_pages * kPage, cudaMemcpyHostToDevice, s));
       h2d += (double)parent_pages * kPage;
     }
@@ -313,7 +296,7 @@ int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const u
   r.ev_up.resize(up_chunks, nullptr);
   if (!in_pinned && n_slots) {
     for (int b = 0; b < 2; b++) {
-      GRIT_CUDA(cudaMallocHost(&r.h_stage_in[b], chunk_bytes));
+      if (int rc = ctx_pin(ctx, kPinRStageIn0 + b, chunk_bytes, &r.h_stage_in[b], err, errlen)) return rc;
       GRIT_CUDA(cudaEventCreateWithFlags(&r.ev_stage[b], cudaEventDisableTiming));
     }
   }
