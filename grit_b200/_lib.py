@@ -79,6 +79,7 @@ SYMBOLS = {
     "grit_unpin_host": (_I, [_P]),
     "grit_pack_dir": (_I, [C.c_char_p, C.c_char_p, C.POINTER(Opts), C.POINTER(Stats)] + _ERR),
     "grit_restore_dir": (_I, [C.c_char_p, C.c_char_p, C.POINTER(Opts), C.POINTER(Stats)] + _ERR),
+    "grit_verify_dir": (_I, [C.c_char_p, C.POINTER(Opts), C.POINTER(Stats)] + _ERR),
     "grit_write_sentinel": (_I, [C.c_char_p, C.c_char_p]),
 }
 

@@ -46,3 +46,12 @@ def CreateSentinelFile(dir, file_name):
     rc = _lib.load().grit_write_sentinel(os.fsencode(dir), os.fsencode(file_name))
     if rc != 0:
         raise GritError(rc, f"cannot create {os.path.join(dir, file_name)}")
+
+
+def VerifyData(packed_dir, **kw):
+    """Checks a packed checkpoint on the PV without restoring it (grit_verify_dir): checksums of the metadata,
+    CRC-32C of every stored page recomputed on the GPU.  Raises GritError (ECRC / EFORMAT) on damage."""
+    lib = _lib.load()
+    o, st, err = _opts(**kw), Stats(), _lib.errbuf()
+    _lib.check(lib.grit_verify_dir(os.fsencode(packed_dir), C.byref(o), C.byref(st), err, len(err)), err)
+    return st.as_dict()

@@ -34,7 +34,7 @@ struct grit_ctx {
     void* p = nullptr;
     size_t cap = 0;
   };
-  Buf dev[24], pin[16];
+  Buf dev[24], pin[20];
 };
 
 namespace grit {
@@ -67,7 +67,7 @@ int ctx_dev(grit_ctx* ctx, int id, size_t bytes, void** out, char* err, size_t e
 int ctx_pin(grit_ctx* ctx, int id, size_t bytes, void** out, char* err, size_t errlen);
 enum DevBuf { kDevIn0 = 0, kDevOut0 = 3, kDevRef = 6, kDevCrc, kDevHash, kDevParentHash, kDevParentCrc,
               kDevRPacked, kDevRRef, kDevRCrc, kDevROut0 = 14, kDevRParent = 17 };
-enum PinBuf { kPinIn0 = 0, kPinOut0 = 3, kPinCounts = 6, kPinMeta0 = 7, kPinRStageOut0 = 10, kPinRStageIn0 = 13 };
+enum PinBuf { kPinIn0 = 0, kPinOut0 = 3, kPinCounts = 6, kPinMeta0 = 7, kPinRStageOut0 = 10, kPinRStageIn0 = 13 /* ..15 */ };
 bool staged_pack();  // true unless GRITPACK_FUSED=1 selects the experimental single-pass pack kernel
 
 }  // namespace grit

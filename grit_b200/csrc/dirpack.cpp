@@ -9,7 +9,8 @@
 // becomes one page stream -- every regular file, in filepath.WalkDir order
 // (copy.go:23), padded with zeros to a 4 KiB multiple -- that goes through the
 // GPU pack pipeline; the PV receives
-//     pages.bin          the pages that had to be stored, in slot order
+//     pages-NNN.bin      the pages that had to be stored: slot order, striped 8 MiB-wise over 8 files
+//                        (a file system takes one writer per file; eight files take eight)
 //     pagemap.bin        u32 ref[n_pages] then u32 crc32c[n_pages]
 //     hashes.bin         u64 hash64[n_pages]   (input of the next incremental pack)
 //     gritpack.manifest  tree layout + sizes + checksums, written last (rename)
@@ -36,7 +37,7 @@ using namespace grit;
 namespace {
 
 constexpr char kMagic[8] = {'G', 'R', 'I', 'T', 'P', 'A', 'K', '1'};
-constexpr uint32_t kFormatVersion = 1;
+constexpr uint32_t kFormatVersion = 2;
 const char* const kManifest = "gritpack.manifest";
 
 struct Entry {
@@ -51,6 +52,7 @@ struct Manifest {
   std::vector<Entry> entries;
   uint64_t n_pages = 0, n_slots = 0, bytes_logical = 0;
   uint32_t pagemap_crc = 0, hashes_crc = 0;
+  uint32_t n_shards = 8, stripe_slots = 2048;  // layout of the stored pages over pages-NNN.bin
   std::string parent;
 };
 
@@ -61,6 +63,24 @@ std::string errno_msg(const char* op, const std::string& path) {
 double now_s() {
   return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
+
+// GRITPACK_DEBUG=1: wall-clock phases of the directory calls on stderr
+struct Phases {
+  const char* what;
+  double last = now_s();
+  std::string line;
+  explicit Phases(const char* w) : what(w) {}
+  void mark(const char* name) {
+    const double t = now_s();
+    char b[64];
+    snprintf(b, sizeof b, " %s %.1f ms,", name, (t - last) * 1e3);
+    line += b;
+    last = t;
+  }
+  ~Phases() {
+    if (getenv("GRITPACK_DEBUG")) fprintf(stderr, "[gritpack] %s:%s\n", what, line.c_str());
+  }
+};
 
 // os.MkdirAll(path, os.ModePerm), copy.go:36
 int mkdir_all(const std::string& path) {
@@ -136,6 +156,8 @@ std::string encode_manifest(const Manifest& m) {
   put<uint64_t>(&b, m.bytes_logical);
   put<uint32_t>(&b, m.pagemap_crc);
   put<uint32_t>(&b, m.hashes_crc);
+  put<uint32_t>(&b, m.n_shards);
+  put<uint32_t>(&b, m.stripe_slots);
   put<uint32_t>(&b, (uint32_t)m.parent.size());
   put(&b, m.parent.data(), m.parent.size());
   for (const auto& e : m.entries) {
@@ -202,7 +224,7 @@ bool has_manifest(const std::string& dir) {
 int load_manifest(const std::string& dir, Manifest* m, std::string* msg) {
   std::string b;
   if (int rc = read_file(dir + "/" + kManifest, &b, msg)) return rc;
-  if (b.size() < 8 + 4 * 2 + 8 * 3 + 4 * 3 + 4 || memcmp(b.data(), kMagic, 8))
+  if (b.size() < 8 + 4 * 2 + 8 * 3 + 4 * 5 + 4 || memcmp(b.data(), kMagic, 8))
     return *msg = dir + ": not a gritpack manifest", GRIT_EFORMAT;
   uint32_t want;
   memcpy(&want, b.data() + b.size() - 4, 4);
@@ -215,6 +237,9 @@ int load_manifest(const std::string& dir, Manifest* m, std::string* msg) {
   m->bytes_logical = r.get<uint64_t>();
   m->pagemap_crc = r.get<uint32_t>();
   m->hashes_crc = r.get<uint32_t>();
+  m->n_shards = r.get<uint32_t>();
+  m->stripe_slots = r.get<uint32_t>();
+  if (m->n_shards == 0 || m->n_shards > 256 || m->stripe_slots == 0) return *msg = dir + ": bad page store layout", GRIT_EFORMAT;
   m->parent = r.str(r.get<uint32_t>());
   for (uint32_t i = 0; i < n_entries && r.ok; i++) {
     Entry e;
@@ -281,6 +306,17 @@ void pieces_for(const std::vector<const Entry*>& files, uint64_t p0, uint64_t p1
   }
 }
 
+// zero the bytes between a file's end and the end of its last page, for the files ending in [p0, p1)
+void zero_tails(const std::vector<const Entry*>& files, uint64_t p0, uint64_t p1, char* buf) {
+  auto it = std::upper_bound(files.begin(), files.end(), p0,
+                             [](uint64_t p, const Entry* e) { return p < e->first_page + e->pages(); });
+  for (; it != files.end() && (*it)->first_page < p1; ++it) {
+    const Entry* e = *it;
+    const uint64_t last = e->first_page + e->pages() - 1, tail = e->size % kPage;
+    if (tail && last >= p0 && last < p1) memset(buf + (last - p0) * kPage + tail, 0, kPage - tail);
+  }
+}
+
 // run fn over the pieces on `threads` threads; first error wins
 template <class Fn>
 int for_pieces(const std::vector<Piece>& ps, unsigned threads, std::string* msg, Fn fn) {
@@ -332,12 +368,104 @@ void write_piece(const std::string& root, const Piece& p, std::string* err) {
   close(fd);
 }
 
+// The stored pages on the PV.  Slot s lives in stripe t = s / stripe, which is stripe number t / k of
+// file pages-(t % k).bin: consecutive stripes go to different files, so a chunk of output is written
+// (and read) by several threads without two of them sharing a file.
+struct PageStore {
+  std::string dir;
+  uint32_t k = 8, stripe = 2048;
+  std::vector<int> fds;
+  ~PageStore() {
+    for (int fd : fds)
+      if (fd >= 0) close(fd);
+  }
+  std::string path(uint32_t i) const {
+    char n[32];
+    snprintf(n, sizeof n, "/pages-%03u.bin", i);
+    return dir + n;
+  }
+  int open_all(bool writing, std::string* msg) {
+    for (uint32_t i = 0; i < k; i++) {
+      const int fd = writing ? open(path(i).c_str(), O_WRONLY | O_CREAT | O_TRUNC | O_CLOEXEC, 0666)
+                             : open(path(i).c_str(), O_RDONLY | O_CLOEXEC);
+      if (fd < 0) return *msg = errno_msg("open", path(i)), GRIT_EIO;
+      fds.push_back(fd);
+    }
+    return GRIT_OK;
+  }
+  // bytes file i holds when the store has n_slots pages
+  uint64_t shard_bytes(uint32_t i, uint64_t n_slots) const {
+    const uint64_t full = n_slots / stripe, rem = n_slots % stripe;
+    uint64_t slots = full / k * stripe + (i < full % k ? stripe : 0);
+    if (i == full % k) slots += rem;
+    return slots * kPage;
+  }
+  int check_sizes(uint64_t n_slots, std::string* msg) const {
+    for (uint32_t i = 0; i < k; i++) {
+      struct stat st;
+      if (fstat(fds[i], &st) != 0 || (uint64_t)st.st_size != shard_bytes(i, n_slots))
+        return *msg = path(i) + ": size does not match the manifest", GRIT_EFORMAT;
+    }
+    return GRIT_OK;
+  }
+  // read or write slots [s0, s0 + n) from / to buf, one piece per stripe, on `threads` threads
+  int io(uint64_t s0, uint64_t n, char* buf, unsigned threads, bool write) const {
+    struct P {
+      int fd;
+      uint64_t off, len;
+      char* buf;
+    };
+    std::vector<P> ps;
+    for (uint64_t s = s0; s < s0 + n;) {
+      const uint64_t t = s / stripe, in = s % stripe, m = std::min<uint64_t>(stripe - in, s0 + n - s);
+      ps.push_back({fds[t % k], (t / k * stripe + in) * kPage, m * kPage, buf + (s - s0) * kPage});
+      s += m;
+    }
+    const unsigned nt = std::max(1u, std::min<unsigned>(threads, (unsigned)ps.size()));
+    std::vector<int> rcs(nt, 0);
+    auto run = [&](unsigned t) {
+      for (size_t i = t; i < ps.size(); i += nt) {
+        uint64_t done = 0;
+        while (done < ps[i].len) {
+          const ssize_t r = write ? pwrite(ps[i].fd, ps[i].buf + done, ps[i].len - done, (off_t)(ps[i].off + done))
+                                  : pread(ps[i].fd, ps[i].buf + done, ps[i].len - done, (off_t)(ps[i].off + done));
+          if (r < 0 && errno == EINTR) continue;
+          if (r <= 0) {
+            rcs[t] = GRIT_EIO;
+            return;
+          }
+          done += (uint64_t)r;
+        }
+      }
+    };
+    std::vector<std::thread> th;
+    for (unsigned t = 1; t < nt; t++) th.emplace_back(run, t);
+    run(0);
+    for (auto& x : th) x.join();
+    for (int rc : rcs)
+      if (rc) return rc;
+    return 0;
+  }
+  int sync_all() const {
+    for (int fd : fds)
+      if (fsync(fd) != 0) return GRIT_EIO;
+    return 0;
+  }
+};
+
 struct Opts {
   int device = 0;
   bool verify = true;
-  unsigned io_threads = 4;
-  uint64_t chunk_pages = (64ull << 20) / kPage;
+  unsigned io_threads = 8;
+  uint64_t chunk_pages = 0;  // 0: chosen from the image size
   std::string parent;
+  // 64 MiB chunks for big images; small images get smaller chunks so that the pinned staging
+  // (six chunks) does not cost more to allocate than the image costs to move
+  uint64_t chunk_for(uint64_t n_pages) const {
+    if (chunk_pages) return chunk_pages;
+    const uint64_t lo = (4ull << 20) / kPage, hi = (64ull << 20) / kPage;
+    return std::min(hi, std::max(lo, (n_pages / 32 + 255) / 256 * 256));
+  }
 };
 
 Opts read_opts(const grit_opts* o) {
@@ -399,35 +527,26 @@ int image_to_device(grit_ctx* ctx, const std::string& dir, int verify, void** d_
     GRIT_CUDA(cudaMalloc(&d_out, std::max<uint64_t>(m.n_pages, 1) * kPage));
     GRIT_CUDA(cudaMalloc(&d_ref, std::max<uint64_t>(m.n_pages, 1) * 4));
     GRIT_CUDA(cudaMalloc(&d_crc, std::max<uint64_t>(m.n_pages, 1) * 4));
-    // pages.bin -> device through a pinned bounce buffer
-    const std::string pages = dir + "/pages.bin";
-    const int fd = open(pages.c_str(), O_RDONLY | O_CLOEXEC);
-    if (fd < 0) return fail(err, errlen, GRIT_EIO, "%s", errno_msg("open", pages).c_str());
+    // stored pages -> device through a pinned bounce buffer
+    PageStore store;
+    store.dir = dir;
+    store.k = m.n_shards;
+    store.stripe = m.stripe_slots;
+    std::string smsg;
+    if (int rc = store.open_all(false, &smsg)) return fail(err, errlen, rc, "%s", smsg.c_str());
+    if (int rc = store.check_sizes(m.n_slots, &smsg)) return fail(err, errlen, rc, "%s", smsg.c_str());
     void* h = nullptr;
-    const uint64_t step = 32ull << 20;
-    if (cudaMallocHost(&h, step) != cudaSuccess) {
-      close(fd);
-      return fail(err, errlen, GRIT_ECUDA, "cudaMallocHost failed");
-    }
+    const uint64_t step = (32ull << 20) / kPage;
+    if (cudaMallocHost(&h, step * kPage) != cudaSuccess) return fail(err, errlen, GRIT_ECUDA, "cudaMallocHost failed");
     int rc = GRIT_OK;
-    for (uint64_t off = 0; off < m.n_slots * kPage && !rc; off += step) {
-      const uint64_t n = std::min(step, m.n_slots * kPage - off);
-      uint64_t done = 0;
-      while (done < n) {
-        const ssize_t k = pread(fd, static_cast<char*>(h) + done, n - done, (off_t)(off + done));
-        if (k < 0 && errno == EINTR) continue;
-        if (k <= 0) {
-          rc = fail(err, errlen, GRIT_EIO, "%s: short read", pages.c_str());
-          break;
-        }
-        done += (uint64_t)k;
-      }
-      if (!rc && cudaMemcpy(static_cast<char*>(d_packed) + off, h, n, cudaMemcpyHostToDevice) != cudaSuccess)
-        rc = fail(err, errlen, GRIT_ECUDA, "H2D of %s failed", pages.c_str());
-      if (stats) stats->h2d_bytes += (double)n;
+    for (uint64_t s0 = 0; s0 < m.n_slots && !rc; s0 += step) {
+      const uint64_t n = std::min(step, m.n_slots - s0);
+      if (store.io(s0, n, static_cast<char*>(h), 8, false)) rc = fail(err, errlen, GRIT_EIO, "%s: short read", dir.c_str());
+      if (!rc && cudaMemcpy(static_cast<char*>(d_packed) + s0 * kPage, h, n * kPage, cudaMemcpyHostToDevice) != cudaSuccess)
+        rc = fail(err, errlen, GRIT_ECUDA, "H2D of the stored pages of %s failed", dir.c_str());
+      if (stats) stats->h2d_bytes += (double)n * kPage;
     }
     cudaFreeHost(h);
-    close(fd);
     if (rc) return rc;
     GRIT_CUDA(cudaMemcpy(d_ref, ref.data(), m.n_pages * 4, cudaMemcpyHostToDevice));
     GRIT_CUDA(cudaMemcpy(d_crc, crc.data(), m.n_pages * 4, cudaMemcpyHostToDevice));
@@ -460,6 +579,7 @@ int grit_pack_dir(const char* src_dir, const char* dst_dir, const grit_opts* opt
                   size_t errlen) {
   if (!src_dir || !dst_dir) return fail(err, errlen, GRIT_EINVAL, "null directory");
   const double t0 = now_s();
+  Phases ph("pack_dir");
   const Opts o = read_opts(opts);
   const std::string src = src_dir, dst = dst_dir;
   std::string msg;
@@ -502,31 +622,30 @@ int grit_pack_dir(const char* src_dir, const char* dst_dir, const grit_opts* opt
   // a re-run (Job retry) must never leave an old manifest vouching for new, partial data
   if (unlink((dst + "/" + kManifest).c_str()) != 0 && errno != ENOENT)
     return fail(err, errlen, GRIT_EIO, "%s", errno_msg("unlink", dst + "/" + kManifest).c_str());
-  const std::string pages_path = dst + "/pages.bin";
-  const int pages_fd = open(pages_path.c_str(), O_WRONLY | O_CREAT | O_TRUNC | O_CLOEXEC, 0666);
-  if (pages_fd < 0) return fail(err, errlen, GRIT_EIO, "%s", errno_msg("open", pages_path).c_str());
-  struct FdGuard {
-    int fd;
-    ~FdGuard() {
-      if (fd >= 0) close(fd);
-    }
-  } pages_guard{pages_fd};
+  PageStore store;
+  store.dir = dst;
+  store.k = m.n_shards;
+  store.stripe = m.stripe_slots;
+  if (int rc = store.open_all(true, &msg)) return fail(err, errlen, rc, "%s", msg.c_str());
 
+  ph.mark("walk+open");
   CtxGuard cg;
   if (int rc = grit_ctx_create(o.device, &cg.ctx, err, errlen)) return rc;
   grit_ctx* ctx = cg.ctx;
+  ph.mark("ctx");
   std::vector<uint32_t> ref(std::max<uint64_t>(m.n_pages, 1)), crc(std::max<uint64_t>(m.n_pages, 1));
   std::vector<uint64_t> hash(std::max<uint64_t>(m.n_pages, 1));
   grit_pack_stats ps{};
   {
-    PackStream pk(ctx, m.n_pages, o.chunk_pages);
+    PackStream pk(ctx, m.n_pages, o.chunk_for(m.n_pages));
     pk.set_outputs(ref.data(), crc.data(), hash.data());
     if (int rc = pk.begin(parent.n_pages ? &parent : nullptr, err, errlen)) return rc;
     if (m.n_pages)
       if (int rc = pk.alloc_staging(true, true, err, errlen)) return rc;
     const uint64_t cp = pk.chunk_pages(), n_chunks = (m.n_pages + cp - 1) / cp;
+    ph.mark("alloc");
 
-    // writer thread: chunk outputs -> pages.bin, in order
+    // writer thread: chunk outputs -> the page store, in order
     struct Job {
       uint64_t chunk, first_slot, n_out;
     };
@@ -550,14 +669,9 @@ int grit_pack_dir(const char* src_dir, const char* dst_dir, const grit_opts* opt
         char e2[256] = "";
         std::string local;
         if (pk.wait_out(j.chunk, e2, sizeof e2)) local = e2;
-        const char* p = static_cast<const char*>(pk.out_buffer(j.chunk));
-        uint64_t done = 0;
-        while (local.empty() && done < j.n_out * kPage) {
-          const ssize_t n = pwrite(pages_fd, p + done, j.n_out * kPage - done, (off_t)(j.first_slot * kPage + done));
-          if (n < 0 && errno == EINTR) continue;
-          if (n <= 0) local = errno_msg("write", pages_path);
-          else done += (uint64_t)n;
-        }
+        if (local.empty() && j.n_out &&
+            store.io(j.first_slot, j.n_out, static_cast<char*>(pk.out_buffer(j.chunk)), o.io_threads, true))
+          local = errno_msg("write", store.dir + "/pages-*.bin");
         {
           std::lock_guard<std::mutex> l(mu);
           if (!local.empty() && werr.empty()) werr = local;
@@ -580,9 +694,9 @@ int grit_pack_dir(const char* src_dir, const char* dst_dir, const grit_opts* opt
         const uint64_t p0 = i * cp, p1 = std::min(m.n_pages, p0 + cp);
         if ((rc = pk.wait_in_free(i, err, errlen))) break;
         char* buf = static_cast<char*>(pk.in_buffer(i));
-        memset(buf, 0, (p1 - p0) * kPage);  // tails of files shorter than a page multiple read as zeros
         std::vector<Piece> pieces;
         pieces_for(files, p0, p1, buf, &pieces);
+        zero_tails(files, p0, p1, buf);  // the rest of a file's last page reads as zeros
         if ((rc = for_pieces(pieces, o.io_threads, &msg, [&](const Piece& p, std::string* e) { read_piece(src, p, e); }))) {
           fail(err, errlen, rc, "%s", msg.c_str());
           break;
@@ -611,13 +725,15 @@ int grit_pack_dir(const char* src_dir, const char* dst_dir, const grit_opts* opt
     stop_writer();
     if (!rc && !werr.empty()) rc = fail(err, errlen, GRIT_EIO, "%s", werr.c_str());
     if (rc) return rc;
+    ph.mark("stream");
     if ((rc = pk.finish(&ps, err, errlen))) return rc;
     st.h2d_bytes = pk.h2d_bytes;
     st.d2h_bytes = pk.d2h_bytes;
   }
   if (ps.n_peer) return fail(err, errlen, GRIT_EINVAL, "internal: peer references in a single-rank pack");
+  ph.mark("finish+free");
   m.n_slots = ps.n_data;
-  if (fsync(pages_fd) != 0) return fail(err, errlen, GRIT_EIO, "%s", errno_msg("fsync", pages_path).c_str());
+  if (store.sync_all()) return fail(err, errlen, GRIT_EIO, "%s", errno_msg("fsync", store.dir + "/pages-*.bin").c_str());
 
   std::string pagemap(m.n_pages * 8, '\0');
   memcpy(&pagemap[0], ref.data(), m.n_pages * 4);
@@ -637,6 +753,7 @@ int grit_pack_dir(const char* src_dir, const char* dst_dir, const grit_opts* opt
     close(dfd);
   }
 
+  ph.mark("metadata+fsync");
   st.bytes_logical = m.bytes_logical;
   st.bytes_stored = m.n_slots * kPage + pagemap.size() + m.n_pages * 8 + enc.size();
   st.n_pages = ps.n_pages;
@@ -651,12 +768,20 @@ int grit_pack_dir(const char* src_dir, const char* dst_dir, const grit_opts* opt
   return GRIT_OK;
 }
 
-int grit_restore_dir(const char* src_dir, const char* dst_dir, const grit_opts* opts, grit_stats* stats, char* err,
-                     size_t errlen) {
-  if (!src_dir || !dst_dir) return fail(err, errlen, GRIT_EINVAL, "null directory");
+}  // extern "C"
+
+namespace {
+
+// grit_restore_dir, and with dst_dir == nullptr grit_verify_dir: the same pipeline with nothing written
+int restore_or_verify(const char* src_dir, const char* dst_dir, const grit_opts* opts, grit_stats* stats, char* err,
+                      size_t errlen) {
+  if (!src_dir) return fail(err, errlen, GRIT_EINVAL, "null directory");
+  const bool writing = dst_dir != nullptr;
   const double t0 = now_s();
-  const Opts o = read_opts(opts);
-  const std::string src = src_dir, dst = dst_dir;
+  Phases ph(writing ? "restore_dir" : "verify_dir");
+  Opts o = read_opts(opts);
+  if (!writing) o.verify = true;
+  const std::string src = src_dir, dst = writing ? dst_dir : "";
   std::string msg;
   grit_stats st{};
   if (!has_manifest(src))
@@ -672,9 +797,11 @@ int grit_restore_dir(const char* src_dir, const char* dst_dir, const grit_opts* 
     if (GRIT_REF_KIND(ref[p]) == GRIT_KIND_PEER)
       return fail(err, errlen, GRIT_EFORMAT, "%s: page %llu refers to a peer rank's image", src_dir, (unsigned long long)p);
 
+  ph.mark("manifest");
   CtxGuard cg;
   if (int rc = grit_ctx_create(o.device, &cg.ctx, err, errlen)) return rc;
   grit_ctx* ctx = cg.ctx;
+  ph.mark("ctx");
 
   void* d_parent = nullptr;
   uint64_t parent_pages = 0;
@@ -688,47 +815,41 @@ int grit_restore_dir(const char* src_dir, const char* dst_dir, const grit_opts* 
   }
 
   // tree skeleton: directories 0777 & ~umask (copy.go:36), files created and sized
-  if (mkdir_all(dst) != 0) return fail(err, errlen, GRIT_EIO, "%s", errno_msg("mkdir", dst).c_str());
+  if (writing && mkdir_all(dst) != 0) return fail(err, errlen, GRIT_EIO, "%s", errno_msg("mkdir", dst).c_str());
   std::vector<const Entry*> files;
   for (const auto& e : m.entries) {
     const std::string path = dst + "/" + e.path;
     if (e.type == 0) {
       st.n_dirs++;
-      if (mkdir_all(path) != 0) return fail(err, errlen, GRIT_EIO, "%s", errno_msg("mkdir", path).c_str());
+      if (writing && mkdir_all(path) != 0) return fail(err, errlen, GRIT_EIO, "%s", errno_msg("mkdir", path).c_str());
       continue;
     }
     st.n_files++;
+    if (!writing) continue;
     const int fd = open(path.c_str(), O_WRONLY | O_CREAT | O_TRUNC | O_CLOEXEC, 0666);  // os.Create, copy.go:73
     if (fd < 0) return fail(err, errlen, GRIT_EIO, "%s", errno_msg("open", path).c_str());
-    const int trc = ftruncate(fd, (off_t)e.size);
+    // reserve the blocks up front: later writes then only overwrite (faster, and no fragmentation on disk)
+    int trc = e.size ? posix_fallocate(fd, 0, (off_t)e.size) : 0;
+    if (trc != 0) trc = ftruncate(fd, (off_t)e.size);  // file systems without fallocate
     close(fd);
     if (trc != 0) return fail(err, errlen, GRIT_EIO, "%s", errno_msg("truncate", path).c_str());
     if (e.size) files.push_back(&e);
   }
 
-  const std::string pages_path = src + "/pages.bin";
-  const int pages_fd = open(pages_path.c_str(), O_RDONLY | O_CLOEXEC);
-  if (pages_fd < 0) return fail(err, errlen, GRIT_EIO, "%s", errno_msg("open", pages_path).c_str());
-  struct FdGuard {
-    int fd;
-    ~FdGuard() { close(fd); }
-  } pages_guard{pages_fd};
-  struct stat pst;
-  if (fstat(pages_fd, &pst) != 0 || (uint64_t)pst.st_size != m.n_slots * kPage)
-    return fail(err, errlen, GRIT_EFORMAT, "%s: size does not match the manifest", pages_path.c_str());
+  ph.mark("skeleton");
+  PageStore store;
+  store.dir = src;
+  store.k = m.n_shards;
+  store.stripe = m.stripe_slots;
+  if (int rc = store.open_all(false, &msg)) return fail(err, errlen, rc, "%s", msg.c_str());
+  if (int rc = store.check_sizes(m.n_slots, &msg)) return fail(err, errlen, rc, "%s", msg.c_str());
 
   RestoreIO io;
-  io.read_packed = [&](uint64_t s0, uint64_t n, void* dstbuf) -> int {
-    uint64_t done = 0;
-    while (done < n * kPage) {
-      const ssize_t k = pread(pages_fd, static_cast<char*>(dstbuf) + done, n * kPage - done, (off_t)(s0 * kPage + done));
-      if (k < 0 && errno == EINTR) continue;
-      if (k <= 0) return GRIT_EIO;
-      done += (uint64_t)k;
-    }
-    return 0;
+  io.read_packed = [&](uint64_t s0, uint64_t n, void* dstbuf) -> int {  // reader thread; split over the I/O threads
+    return store.io(s0, n, static_cast<char*>(dstbuf), o.io_threads, false);
   };
   io.write_out = [&](uint64_t p0, uint64_t p1, const void* srcbuf) -> int {
+    if (!writing) return 0;  // verify only: the CRC check happened on the GPU, the bytes are dropped
     std::vector<Piece> pieces;
     pieces_for(files, p0, p1, const_cast<char*>(static_cast<const char*>(srcbuf)), &pieces);
     return for_pieces(pieces, o.io_threads, &msg, [&](const Piece& p, std::string* e) { write_piece(dst, p, e); });
@@ -737,7 +858,7 @@ int grit_restore_dir(const char* src_dir, const char* dst_dir, const grit_opts* 
   {
     std::lock_guard<std::mutex> g(ctx->mu);
     const int rc = restore_stream(ctx, io, m.n_slots, ref.data(), crc.data(), m.n_pages, d_parent, parent_pages, true,
-                                  o.verify, o.chunk_pages, &rs, &st.h2d_bytes, &st.d2h_bytes, err, errlen);
+                                  o.verify, o.chunk_for(m.n_pages), &rs, &st.h2d_bytes, &st.d2h_bytes, err, errlen);
     st.n_bad += rs.n_bad;
     if (rc) {
       if (!msg.empty() && err && errlen) snprintf(err, errlen, "%s", msg.c_str());
@@ -745,10 +866,11 @@ int grit_restore_dir(const char* src_dir, const char* dst_dir, const grit_opts* 
       return rc;
     }
   }
+  ph.mark("stream");
   // os.Chmod(dstFile, info.Mode()), copy.go:84-89; then make the bytes durable before
   // the caller writes the sentinel that patched containerd polls for (restore.go:20)
   for (const auto& e : m.entries) {
-    if (e.type != 1) continue;
+    if (e.type != 1 || !writing) continue;
     const std::string path = dst + "/" + e.path;
     const int fd = open(path.c_str(), O_WRONLY | O_CLOEXEC);
     if (fd < 0) return fail(err, errlen, GRIT_EIO, "%s", errno_msg("open", path).c_str());
@@ -757,6 +879,7 @@ int grit_restore_dir(const char* src_dir, const char* dst_dir, const grit_opts* 
     if (r1 != 0 || r2 != 0) return fail(err, errlen, GRIT_EIO, "%s", errno_msg("chmod", path).c_str());
   }
 
+  ph.mark("fsync+chmod");
   st.bytes_logical = m.bytes_logical;
   st.bytes_stored = m.n_slots * kPage;
   st.n_pages = m.n_pages;
@@ -773,6 +896,20 @@ int grit_restore_dir(const char* src_dir, const char* dst_dir, const grit_opts* 
   st.seconds = now_s() - t0;
   if (stats) *stats = st;
   return GRIT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int grit_restore_dir(const char* src_dir, const char* dst_dir, const grit_opts* opts, grit_stats* stats, char* err,
+                     size_t errlen) {
+  if (!dst_dir) return fail(err, errlen, GRIT_EINVAL, "null directory");
+  return restore_or_verify(src_dir, dst_dir, opts, stats, err, errlen);
+}
+
+int grit_verify_dir(const char* src_dir, const grit_opts* opts, grit_stats* stats, char* err, size_t errlen) {
+  return restore_or_verify(src_dir, nullptr, opts, stats, err, errlen);
 }
 
 }  // extern "C"

@@ -4,8 +4,11 @@
 
 #include <algorithm>
 #include <chrono>
+#include <condition_variable>
 #include <cstdlib>
 #include <cstring>
+#include <deque>
+#include <thread>
 
 using namespace grit;
 
@@ -241,18 +244,18 @@ int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const u
 
   struct Res {
     void *d_packed = nullptr, *d_parent = nullptr, *d_out[kPipeDepth] = {}, *h_stage_out[kPipeDepth] = {};
-    void* h_stage_in[2] = {};
+    void* h_stage_in[3] = {};
     uint32_t *d_ref = nullptr, *d_crc = nullptr;
     cudaEvent_t ev_kern[kPipeDepth] = {}, ev_d2h[kPipeDepth] = {};
     std::vector<cudaEvent_t> ev_up;
-    cudaEvent_t ev_stage[2] = {};
+    cudaEvent_t ev_stage[3] = {};
     ~Res() {
       cudaDeviceSynchronize();  // nothing of this call may still be running when the cached buffers are reused
       for (int b = 0; b < kPipeDepth; b++) {
         if (ev_kern[b]) cudaEventDestroy(ev_kern[b]);
         if (ev_d2h[b]) cudaEventDestroy(ev_d2h[b]);
       }
-      for (int b = 0; b < 2; b++)
+      for (int b = 0; b < 3; b++)
         if (ev_stage[b]) cudaEventDestroy(ev_stage[b]);
       for (auto e : ev_up) cudaEventDestroy(e);
     }
@@ -294,26 +297,102 @@ int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const u
   // upload the packed pages in chunks on the copy stream, one event per chunk
   const uint64_t up_chunks = (n_slots + chunk_pages - 1) / chunk_pages;
   r.ev_up.resize(up_chunks, nullptr);
+  constexpr int kStageIn = 3;
   if (!in_pinned && n_slots) {
-    for (int b = 0; b < 2; b++) {
+    for (int b = 0; b < kStageIn; b++) {
       if (int rc = ctx_pin(ctx, kPinRStageIn0 + b, chunk_bytes, &r.h_stage_in[b], err, errlen)) return rc;
       GRIT_CUDA(cudaEventCreateWithFlags(&r.ev_stage[b], cudaEventDisableTiming));
     }
   }
+
+  // Callback I/O runs on two helper threads so that reading packed pages, the GPU pipeline and
+  // writing restored pages overlap: the reader keeps the staging-in buffers full ahead of the
+  // upload, the writer drains staging-out buffers as their D2H copies land.
+  struct Helpers {
+    std::mutex mu;
+    std::condition_variable cv;
+    uint64_t filled = 0, consumed = 0;  // reader: chunks read / chunks whose H2D is enqueued
+    struct Job {
+      uint64_t p0, p1;
+      int b;
+    };
+    std::deque<Job> jobs;  // writer
+    uint64_t written = 0;
+    int rc = 0;
+    bool stop = false;
+    std::thread reader, writer;
+    ~Helpers() {
+      {
+        std::lock_guard<std::mutex> l(mu);
+        stop = true;
+      }
+      cv.notify_all();
+      if (reader.joinable()) reader.join();
+      if (writer.joinable()) writer.join();
+    }
+  } hp;
+  if (!in_pinned && up_chunks)
+    hp.reader = std::thread([&] {
+      cudaSetDevice(ctx->device);
+      for (uint64_t c = 0; c < up_chunks; c++) {
+        const int b = (int)(c % kStageIn);
+        if (c >= (uint64_t)kStageIn) {  // the slot's previous chunk must have left for the device
+          std::unique_lock<std::mutex> l(hp.mu);
+          hp.cv.wait(l, [&] { return hp.stop || hp.consumed > c - kStageIn; });
+          if (hp.stop) return;
+          l.unlock();
+          cudaEventSynchronize(r.ev_stage[b]);
+        }
+        const uint64_t s0 = c * chunk_pages, n = std::min(chunk_pages, n_slots - s0);
+        const int rc = io.read_packed(s0, n, r.h_stage_in[b]);
+        std::lock_guard<std::mutex> l(hp.mu);
+        if (rc && !hp.rc) hp.rc = rc;
+        hp.filled = c + 1;
+        hp.cv.notify_all();
+        if (rc) return;
+      }
+    });
+  if (!out_pinned && n_chunks)
+    hp.writer = std::thread([&] {
+      cudaSetDevice(ctx->device);
+      for (;;) {
+        Helpers::Job j;
+        {
+          std::unique_lock<std::mutex> l(hp.mu);
+          hp.cv.wait(l, [&] { return hp.stop || !hp.jobs.empty(); });
+          if (hp.jobs.empty()) return;
+          j = hp.jobs.front();
+          hp.jobs.pop_front();
+        }
+        int rc = cudaEventSynchronize(r.ev_d2h[j.b]) == cudaSuccess ? 0 : GRIT_ECUDA;
+        if (!rc) rc = io.write_out(j.p0, j.p1, r.h_stage_out[j.b]);
+        std::lock_guard<std::mutex> l(hp.mu);
+        if (rc && !hp.rc) hp.rc = rc;
+        hp.written++;
+        hp.cv.notify_all();
+      }
+    });
+
   uint64_t uploaded = 0;  // upload chunks enqueued so far
   auto upload_until = [&](uint64_t slot_end) -> int {
     const uint64_t need = std::min(up_chunks, (slot_end + chunk_pages - 1) / chunk_pages);
     for (; uploaded < need; uploaded++) {
       const uint64_t s0 = uploaded * chunk_pages, n = std::min(chunk_pages, n_slots - s0);
       const char* src = static_cast<const char*>(h_packed) + s0 * kPage;
-      if (!in_pinned) {  // no pinned source: the caller fills pinned staging
-        const int b = (int)(uploaded & 1);
-        if (uploaded >= 2) GRIT_CUDA(cudaEventSynchronize(r.ev_stage[b]));
-        if (int rc = io.read_packed(s0, n, r.h_stage_in[b])) return fail(err, errlen, rc, "reading packed pages failed");
+      const int b = (int)(uploaded % kStageIn);
+      if (!in_pinned) {  // no pinned source: the reader thread fills pinned staging
+        std::unique_lock<std::mutex> l(hp.mu);
+        hp.cv.wait(l, [&] { return hp.rc || hp.filled > uploaded; });
+        if (hp.rc) return fail(err, errlen, hp.rc, "reading packed pages failed");
         src = static_cast<const char*>(r.h_stage_in[b]);
       }
       GRIT_CUDA(cudaMemcpyAsync(static_cast<char*>(r.d_packed) + s0 * kPage, src, n * kPage, cudaMemcpyHostToDevice, ctx->h2d));
-      if (!in_pinned) GRIT_CUDA(cudaEventRecord(r.ev_stage[uploaded & 1], ctx->h2d));
+      if (!in_pinned) {
+        GRIT_CUDA(cudaEventRecord(r.ev_stage[b], ctx->h2d));
+        std::lock_guard<std::mutex> l(hp.mu);
+        hp.consumed = uploaded + 1;
+        hp.cv.notify_all();
+      }
       GRIT_CUDA(cudaEventCreateWithFlags(&r.ev_up[uploaded], cudaEventDisableTiming));
       GRIT_CUDA(cudaEventRecord(r.ev_up[uploaded], ctx->h2d));
       h2d += (double)n * kPage;
@@ -324,32 +403,35 @@ int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const u
   GRIT_CUDA(cudaEventRecord(ctx->ev0, s));
   const double t_loop = wall();
   uint64_t slot_front = 0;  // slots referenced by pages before the current chunk end
-  for (uint64_t i = 0; i < n_chunks + 1; i++) {
-    if (i < n_chunks) {
-      const int b = (int)(i % kPipeDepth);
-      const uint64_t p0 = i * chunk_pages, p1 = std::min(n_pages, p0 + chunk_pages);
-      for (uint64_t p = p0; p < p1; p++)
-        if (GRIT_REF_KIND(h_ref[p]) == GRIT_KIND_DATA) slot_front = std::max<uint64_t>(slot_front, GRIT_REF_VALUE(h_ref[p]) + 1);
-      if (int rc = upload_until(std::min(slot_front, n_slots))) return rc;
-      if (uploaded) GRIT_CUDA(cudaStreamWaitEvent(s, r.ev_up[uploaded - 1], 0));
-      if (i >= (uint64_t)kPipeDepth) GRIT_CUDA(cudaStreamWaitEvent(s, r.ev_d2h[b], 0));
-      GRIT_CUDA(launch_restore(ctx->geom, ctx->d_tables, r.d_packed, n_slots, r.d_ref, r.d_crc, n_pages, p0, p1, imgs,
-                               r.d_out[b], verify, ctx->d_cnt, s));
-      ctx->launches++;
-      GRIT_CUDA(cudaEventRecord(r.ev_kern[b], s));
-      GRIT_CUDA(cudaStreamWaitEvent(ctx->d2h, r.ev_kern[b], 0));
-      char* dst = static_cast<char*>(h_out) + p0 * kPage;
-      if (!out_pinned) {
-        if (i >= (uint64_t)kPipeDepth) {  // staging buffer b still holds chunk i - depth
-          GRIT_CUDA(cudaEventSynchronize(r.ev_d2h[b]));
-          const uint64_t q0 = (i - kPipeDepth) * chunk_pages;
-          if (int rc = io.write_out(q0, q0 + chunk_pages, r.h_stage_out[b])) return fail(err, errlen, rc, "writing restored pages failed");
-        }
-        dst = static_cast<char*>(r.h_stage_out[b]);
+  for (uint64_t i = 0; i < n_chunks; i++) {
+    const int b = (int)(i % kPipeDepth);
+    const uint64_t p0 = i * chunk_pages, p1 = std::min(n_pages, p0 + chunk_pages);
+    for (uint64_t p = p0; p < p1; p++)
+      if (GRIT_REF_KIND(h_ref[p]) == GRIT_KIND_DATA) slot_front = std::max<uint64_t>(slot_front, GRIT_REF_VALUE(h_ref[p]) + 1);
+    if (int rc = upload_until(std::min(slot_front, n_slots))) return rc;
+    if (uploaded) GRIT_CUDA(cudaStreamWaitEvent(s, r.ev_up[uploaded - 1], 0));
+    if (i >= (uint64_t)kPipeDepth) GRIT_CUDA(cudaStreamWaitEvent(s, r.ev_d2h[b], 0));
+    GRIT_CUDA(launch_restore(ctx->geom, ctx->d_tables, r.d_packed, n_slots, r.d_ref, r.d_crc, n_pages, p0, p1, imgs,
+                             r.d_out[b], verify, ctx->d_cnt, s));
+    ctx->launches++;
+    GRIT_CUDA(cudaEventRecord(r.ev_kern[b], s));
+    GRIT_CUDA(cudaStreamWaitEvent(ctx->d2h, r.ev_kern[b], 0));
+    char* dst = static_cast<char*>(h_out) + p0 * kPage;
+    if (!out_pinned) {
+      if (i >= (uint64_t)kPipeDepth) {  // staging buffer b still holds chunk i - depth until the writer is done with it
+        std::unique_lock<std::mutex> l(hp.mu);
+        hp.cv.wait(l, [&] { return hp.rc || hp.written > i - kPipeDepth; });
+        if (hp.rc) return fail(err, errlen, hp.rc, "writing restored pages failed");
       }
-      GRIT_CUDA(cudaMemcpyAsync(dst, r.d_out[b], (p1 - p0) * kPage, cudaMemcpyDeviceToHost, ctx->d2h));
-      GRIT_CUDA(cudaEventRecord(r.ev_d2h[b], ctx->d2h));
-      d2h += (double)(p1 - p0) * kPage;
+      dst = static_cast<char*>(r.h_stage_out[b]);
+    }
+    GRIT_CUDA(cudaMemcpyAsync(dst, r.d_out[b], (p1 - p0) * kPage, cudaMemcpyDeviceToHost, ctx->d2h));
+    GRIT_CUDA(cudaEventRecord(r.ev_d2h[b], ctx->d2h));
+    d2h += (double)(p1 - p0) * kPage;
+    if (!out_pinned) {
+      std::lock_guard<std::mutex> l(hp.mu);
+      hp.jobs.push_back({p0, p1, b});
+      hp.cv.notify_all();
     }
   }
   if (int rc = upload_until(n_slots)) return rc;  // nothing may be left half-sent
@@ -357,12 +439,10 @@ int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const u
   if (int rc = read_counters(ctx, s, err, errlen)) return rc;
   GRIT_CUDA(cudaStreamSynchronize(ctx->d2h));
   GRIT_CUDA(cudaStreamSynchronize(ctx->h2d));
-  if (!out_pinned) {  // drain the staged tail
-    const uint64_t first = n_chunks > (uint64_t)kPipeDepth ? n_chunks - kPipeDepth : 0;
-    for (uint64_t i = first; i < n_chunks; i++) {
-      const uint64_t p0 = i * chunk_pages, p1 = std::min(n_pages, p0 + chunk_pages);
-      if (int rc = io.write_out(p0, p1, r.h_stage_out[i % kPipeDepth])) return fail(err, errlen, rc, "writing restored pages failed");
-    }
+  if (!out_pinned) {  // the writer finishes the tail
+    std::unique_lock<std::mutex> l(hp.mu);
+    hp.cv.wait(l, [&] { return hp.rc || hp.written == n_chunks; });
+    if (hp.rc) return fail(err, errlen, hp.rc, "writing restored pages failed");
   }
   if (h2d_total) *h2d_total += h2d;
   if (d2h_total) *d2h_total += d2h;

@@ -75,7 +75,7 @@ typedef struct grit_opts {
   uint32_t struct_size; /* sizeof(grit_opts), for ABI growth                   */
   int32_t device;       /* CUDA device ordinal                                 */
   uint32_t verify;      /* restore: recompute and compare every page's CRC-32C */
-  uint32_t io_threads;  /* file reader/writer threads, 0 = default (4)         */
+  uint32_t io_threads;  /* file reader/writer threads, 0 = default (8)         */
   uint64_t chunk_bytes; /* pipeline chunk, 0 = default (64 MiB)                */
   const char *parent_dir; /* previous packed checkpoint for incremental, or NULL */
 } grit_opts;
@@ -232,6 +232,15 @@ int grit_pack_dir(const char *src_dir, const char *dst_dir,
 int grit_restore_dir(const char *src_dir, const char *dst_dir,
                      const grit_opts *opts, grit_stats *stats, char *err,
                      size_t errlen);
+
+/* Checks a packed directory and writes nothing: manifest and page-map checksums
+ * on the host, then the whole restore pipeline (parents included) with every
+ * stored page's CRC-32C recomputed on the GPU and the restored bytes dropped.
+ * Returns GRIT_ECRC / GRIT_EFORMAT like grit_restore_dir would.  The reference
+ * never verifies what it copied (copy.go:66-90); this is the "gritpack verify"
+ * step of SURVEY 8(f). */
+int grit_verify_dir(const char *src_dir, const grit_opts *opts,
+                    grit_stats *stats, char *err, size_t errlen);
 
 /* CreateSentinelFile (copy.go:92-102): dir/name holding "Transfer Completed\n". */
 int grit_write_sentinel(const char *dir, const char *name);

@@ -14,6 +14,18 @@ def u32(t):
     return t.numpy().view(np.uint32)
 
 
+def read_page_store(pv, n_slots, k=8, stripe=2048):
+    """The stored pages in slot order, reassembled from the striped pages-NNN.bin files."""
+    shards = [np.fromfile(os.path.join(pv, f"pages-{i:03d}.bin"), np.uint8) for i in range(k)]
+    out = np.empty(n_slots * PAGE, np.uint8)
+    for t in range((n_slots + stripe - 1) // stripe):
+        n = min(stripe, n_slots - t * stripe)
+        off = (t // k) * stripe * PAGE
+        out[t * stripe * PAGE:(t * stripe + n) * PAGE] = shards[t % k][off:off + n * PAGE]
+    assert sum(s.size for s in shards) == n_slots * PAGE
+    return out
+
+
 @pytest.mark.parametrize("pinned", [True, False])
 @pytest.mark.parametrize("n_pages", [1, 1000, 40000])     # 40000 pages = 3 pipeline chunks of 64 MiB
 def test_pack_host_matches_oracle(ctx, oracle, pinned, n_pages):
@@ -102,9 +114,13 @@ def test_restore_dir_refuses_incomplete_or_corrupt_images(oracle, tmp_path):
     src.mkdir()
     make_criu_tree(str(src), oracle, big_pages=500)
     copy.TransferData(str(src), str(pv), copy.UPLOAD)
-    with open(pv / "pages.bin", "r+b") as f:
+    assert copy.VerifyData(str(pv))["n_bad"] == 0 and not host.exists()      # verify writes nothing
+    with open(pv / "pages-000.bin", "r+b") as f:     # slot 40 lives in the first stripe of the first shard
         f.seek(40 * PAGE + 3)
         f.write(b"\xAA\xBB")
+    with pytest.raises(_lib.GritError) as e:
+        copy.VerifyData(str(pv))
+    assert e.value.code == _lib.ECRC and not host.exists()
     with pytest.raises(_lib.GritError) as e:
         copy.TransferData(str(pv), str(host), copy.DOWNLOAD)
     assert e.value.code == _lib.ECRC
@@ -122,3 +138,53 @@ def test_empty_directory(tmp_path):
     copy.TransferData(str(src), str(pv), copy.UPLOAD)
     copy.TransferData(str(pv), str(host), copy.DOWNLOAD)
     assert tree_snapshot(str(host)) == tree_snapshot(str(src))
+
+
+def test_config0_one_gib_criu_directory(oracle, tmp_path):
+    """BASELINE configs[0]: the synthetic 1 GiB CRIU image dir, packed to a local path and restored, against the
+    reference copy path restated.  Page-class counts must match the oracle's pack of the same page stream."""
+    import shutil
+    from criu_tree import build_c1_tree
+    from grit_b200 import agent
+    base = "/dev/shm" if os.path.isdir("/dev/shm") else str(tmp_path)
+    root = os.path.join(base, f"grit_c1_{os.getpid()}")
+    try:
+        src, pv, host, ref = (os.path.join(root, n) for n in ("src", "pv", "host", "ref"))
+        os.makedirs(src)
+        total = build_c1_tree(src, oracle)
+        assert total == 1 << 30
+        st = agent.RunCheckpoint(agent.GritAgentOptions("checkpoint", src, pv))
+        assert st["bytes_logical"] == 1 << 30 and st["n_files"] == 31
+        assert 0.08 < st["n_zero"] / st["n_pages"] < 0.12 and 0.12 < st["n_dup"] / st["n_pages"] < 0.17
+        # the oracle packs the same page stream (files in walk order, zero padded) to the same references
+        stream = bytearray()
+        for d, dirs, files in os.walk(src):
+            dirs.sort()
+        paths = sorted(os.path.relpath(os.path.join(d, f), src) for d, _, fs in os.walk(src) for f in fs)
+        # filepath.WalkDir order: lexical per directory level; os.walk + per-level sort gives the same for this tree
+        order = []
+
+        def walk(rel):
+            full = os.path.join(src, rel) if rel else src
+            for n in sorted(os.listdir(full)):
+                r = os.path.join(rel, n) if rel else n
+                if os.path.isdir(os.path.join(src, r)):
+                    walk(r)
+                else:
+                    order.append(r)
+        walk("")
+        assert sorted(order) == paths
+        for r in order:
+            b = open(os.path.join(src, r), "rb").read()
+            stream += b + bytes(-len(b) % PAGE)
+        o = oracle.pack(np.frombuffer(bytes(stream), np.uint8), threads=8)
+        for k in ("n_pages", "n_zero", "n_data", "n_dup"):
+            assert st[k] == o["stats"][k], k
+        pm = np.fromfile(os.path.join(pv, "pagemap.bin"), np.uint32)
+        assert np.array_equal(pm[: o["ref"].size], o["ref"]) and np.array_equal(pm[o["ref"].size:], o["crc"])
+        assert np.array_equal(read_page_store(pv, o["stats"]["n_data"]), o["packed"])
+        agent.RunRestore(agent.GritAgentOptions("restore", pv, host))
+        assert oracle.transfer_data(src, ref)[0] == 0 and oracle.create_sentinel_file(ref, "download-state") == 0
+        assert tree_snapshot(host) == tree_snapshot(ref)
+    finally:
+        shutil.rmtree(root, ignore_errors=True)
