@@ -136,7 +136,7 @@ int PackStream::submit(uint64_t i, const void* h_src, uint64_t n_pages, char* er
   }
   const uint64_t tile = staged_pack() ? kCompactTile : fused_tile_pages();
   GRIT_CUDA(cudaMemsetAsync(ctx_->d_status, 0, (n_pages + tile - 1) / tile * sizeof(unsigned long long), s));
-  GRIT_CUDA(cudaMemsetAsync(&ctx_->d_cnt->ticket, 0, sizeof(unsigned int), s));
+  GRIT_CUDA(cudaMemsetAsync(&ctx_->d_cnt->ticket, 0, 3 * sizeof(unsigned int), s));  // ticket, copy_ticket, watermark
   if (staged_pack()) {
     GRIT_CUDA(launch_analyze(ctx_->geom, ctx_->d_tables, d_in_[b], n_pages, d_crc_ + p0, d_hash_ + p0, d_ref_ + p0, s));
     GRIT_CUDA(launch_table_insert(ctx_->geom, table_, d_hash_ + p0, d_ref_ + p0, n_pages, kOriginSelf, p0, s));

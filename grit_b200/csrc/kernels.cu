@@ -465,37 +465,30 @@ k_compact(const uint4* __restrict__ image, uint64_t n_pages, uint32_t* __restric
 }
 
 // ------------------------------------------------------------------ K1+K2+K3 fused
-// One pass over the image.  The sixteen warps of a CTA form kGroups independent groups that share
-// the CRC tables; each group takes tiles by ticket and runs, per tile,
-//   A  analyze the pages (HBM -> registers, lines kept in L2), write crc/hash, enter non-zero
-//      hashes in the table
-//   B  publish INSERTED; wait until every earlier tile has inserted too (then the table's minimum
-//      for each of this tile's hashes is final); decide each page's reference; publish the number
-//      of pages to store; decoupled look-back over earlier tiles for the tile's first slot
-//   C  copy the pages to store into the packed image -- read microseconds ago, so these reads hit
-//      L2 and DRAM sees the image once (N read + U written).
-// Groups only synchronise within themselves (named barriers), so on every SM the waits and copies
-// of one group overlap the CRC arithmetic of the others.  All waits are on lower tile numbers,
-// ticketed earlier by groups that are resident (grid <= SM count, one CTA per SM), so they end.
-#ifndef GRIT_FUSED_GROUPS
-#define GRIT_FUSED_GROUPS 2
-#endif
-#ifndef GRIT_FUSED_ROUNDS
-#define GRIT_FUSED_ROUNDS 2
-#endif
-constexpr int kGroups = GRIT_FUSED_GROUPS;
-constexpr int kGroupWarps = kWarps / kGroups;
-constexpr int kGroupThreads = kGroupWarps * 32;
-constexpr int kFusedRounds = GRIT_FUSED_ROUNDS;
-constexpr int kFusedTile = kGroupWarps * 4 * kFusedRounds;  // pages per group tile
-constexpr int kTileWarps = (kFusedTile + 31) / 32;          // warps that hold one page per lane in B
-static_assert(kFusedTile <= kGroupThreads, "one thread per page in the resolve step");
+// One pass over the image with two kinds of jobs on 128-page tiles, handed to whichever CTA is
+// free (persistent grid, one CTA per SM):
+//   ANALYZE(t)  K1 on tile t (HBM -> registers), crc/hash written, non-zero hashes entered in the
+//               table, the page's table slot parked in ref[]; then status[t] = INSERTED.
+//   COPY(c)     only taken once every tile <= c is INSERTED (so the table's minimum for each of
+//               c's hashes is final) and in tile order: decide the references, publish the count
+//               of pages to store, decoupled look-back over earlier COPY jobs for the first slot,
+//               copy the stored pages into the packed image.  The tile was analysed microseconds
+//               ago, so these reads should hit L2 and DRAM sees the image once (N read + U written).
+// COPY has priority, so the distance between a tile's two reads stays short.  No job ever waits for
+// a job that is not already running: ANALYZE waits for nothing, COPY(c) looks back at COPY jobs
+// claimed before it.  CTAs without a job poll.
+constexpr int kFusedRounds = 2;
+constexpr int kFusedTile = kWarps * 4 * kFusedRounds;  // 128 pages = 512 KiB
 constexpr unsigned long long kStInserted = 1ull << 62, kStAgg = 2ull << 62, kStPrefix = 3ull << 62;
-constexpr uint32_t kTsZero = 0xFFFFFFFFu, kTsAbsent = 0xFFFFFFFEu;
+constexpr uint32_t kJobAnalyze = 0, kJobCopy = 1, kJobRetry = 2, kJobExit = 3;
+constexpr uint32_t kNoTile = 0xFFFFFFFFu;
+constexpr uint32_t kMaxLead = 192;  // ANALYZE may run at most this many tiles ahead of COPY (L2 residency)
 
 __device__ __forceinline__ uint32_t ld_cg_u32(const uint32_t* p) { return __ldcg(p); }
-__device__ __forceinline__ void group_sync(uint32_t grp) {
-  asm volatile("bar.sync %0, %1;" ::"r"(grp + 1), "r"(kGroupThreads) : "memory");
+__device__ __forceinline__ uint32_t ld_relaxed_u32(const unsigned int* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
 }
 
 __global__ void __launch_bounds__(kThreads, 1)
@@ -503,58 +496,103 @@ k_pack_fused(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ image
              uint32_t* __restrict__ crc, unsigned long long* __restrict__ hash, uint32_t* __restrict__ ref,
              DedupTable t, PeerCrcs crcs, uint4* __restrict__ packed, uint64_t capacity_pages, uint64_t slot_base,
              int chained, unsigned long long* __restrict__ status, DevCounters* __restrict__ cnt) {
-  __shared__ uint32_t s_tile[kGroups][2], s_excl[kGroups], s_warp_cnt[kGroups][kTileWarps], s_ts[kGroups][kFusedTile];
-  __shared__ uint16_t s_list[kGroups][kFusedTile];
+  __shared__ uint32_t s_job, s_tile, s_excl, s_warp_cnt[4];
+  __shared__ uint16_t s_list[kFusedTile];
   load_tables(tabs);
   const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const uint32_t grp = warp / kGroupWarps, gw = warp % kGroupWarps, gt = threadIdx.x - grp * kGroupThreads;
   const uint32_t g = lane >> 3, l = lane & 7, lane4 = lane * 4;
   const uint32_t n_tiles = (uint32_t)((n_pages + kFusedTile - 1) / kFusedTile);
   const uint64_t ref_base = chained ? cnt->slot_base : slot_base;
   const uint64_t out_base = chained ? 0 : slot_base;
   const uint64_t keep_in_l2 = policy_evict_last(), done_with = policy_evict_first();
   uint32_t n_kind[5] = {0, 0, 0, 0, 0};  // this thread's page counts per kind
+  uint32_t pending = kNoTile;             // warp 0: a COPY ticket taken before its tile was ready
 
-  if (gt == 0) s_tile[grp][0] = atomicAdd(&cnt->ticket, 1u);
-  group_sync(grp);
-  uint32_t tile = s_tile[grp][0];
-  uint4 ring[kRing];
-  if (tile < n_tiles) {
-    const uint64_t p = (uint64_t)tile * kFusedTile + gw * 4 + g;
-    ring_fill<true>(ring, image + p * 256 + l, p < n_pages, keep_in_l2);
-  }
-  for (uint32_t it = 1; tile < n_tiles; it++) {
-    // the next ticket is taken now so that the load ring can run on into the next tile
-    if (gt == 0) s_tile[grp][it & 1] = atomicAdd(&cnt->ticket, 1u);
-    group_sync(grp);
-    const uint32_t next_tile = s_tile[grp][it & 1];
+  for (;;) {
+    // ---- pick a job (warp 0): a COPY if one is ready, else an ANALYZE.  COPY tickets are taken with
+    // an atomicAdd as soon as some tile is ready; a ticket that overshoots the watermark is kept
+    // (`pending`) and this CTA analyses other tiles until its tile is ready.
+    if (warp == 0) {
+      uint32_t job = kJobRetry, tile = 0;
+      uint32_t w = ld_relaxed_u32(&cnt->watermark);
+      for (;;) {  // advance the watermark over every tile that has published INSERTED
+        const uint32_t idx = w + lane;
+        const bool ins = idx < n_tiles && (ld_status(&status[idx]) >> 62) != 0;
+        const uint32_t nb = ~__ballot_sync(0xFFFFFFFFu, ins);
+        const uint32_t run = nb ? (uint32_t)__ffs(nb) - 1u : 32u;  // leading INSERTED tiles, 0..32
+        w += run;
+        if (run < 32) break;
+      }
+      if (lane == 0) atomicMax(&cnt->watermark, w);
+      uint32_t c = ld_relaxed_u32(&cnt->copy_ticket);
+      if (pending == kNoTile && c < n_tiles && c < w) {
+        uint32_t tk = 0;
+        if (lane == 0) tk = atomicAdd(&cnt->copy_ticket, 1u);
+        tk = __shfl_sync(0xFFFFFFFFu, tk, 0);
+        if (tk < n_tiles) pending = tk;
+        c = tk + 1;
+      }
+      if (pending != kNoTile && pending < w) {
+        job = kJobCopy;
+        tile = pending;
+        pending = kNoTile;
+      } else {
+        const uint32_t a = ld_relaxed_u32(&cnt->ticket);
+        if (a < n_tiles) {
+          if (a < c + kMaxLead) {
+            uint32_t tk = 0;
+            if (lane == 0) tk = atomicAdd(&cnt->ticket, 1u);
+            tk = __shfl_sync(0xFFFFFFFFu, tk, 0);
+            if (tk < n_tiles) {
+              job = kJobAnalyze;
+              tile = tk;
+            }
+          }
+        } else if (pending == kNoTile && c >= n_tiles) {
+          job = kJobExit;
+        }
+      }
+      if (lane == 0) {
+        s_job = job;
+        s_tile = tile;
+      }
+    }
+    __syncthreads();
+    const uint32_t job = s_job, tile = s_tile;
+    __syncthreads();  // s_job / s_tile may be rewritten as soon as every thread has read them
+    if (job == kJobExit) break;
+    if (job == kJobRetry) {
+      __nanosleep(200);
+      continue;
+    }
     const uint64_t base = (uint64_t)tile * kFusedTile;  // first page of the tile, chunk-local
 
-    // ---- A: analyze + insert
-    static_for<0, kFusedRounds>([&](auto rc) {
-      constexpr int r = decltype(rc)::value;
-      const uint64_t p = base + r * (kGroupWarps * 4) + gw * 4 + g;
-      const bool on = p < n_pages;
-      const uint64_t p_next = (r + 1 < kFusedRounds) ? p + kGroupWarps * 4 : (uint64_t)next_tile * kFusedTile + gw * 4 + g;
-      const bool next_on = ((r + 1 < kFusedRounds) || next_tile < n_tiles) && p_next < n_pages;
-      PageAcc a;
-      a.z = 0;
-      a.h = 0;
-      page_pass<true, true, true>(a, ring, image + p * 256 + l, on, image + p_next * 256 + l, next_on, lane4,
-                                  [](auto, const uint4&) {}, keep_in_l2);
-      const uint32_t page_crc = finish_crc(a, l);
-      uint32_t z = a.z;
-      z |= __shfl_xor_sync(0xFFFFFFFFu, z, 1);
-      z |= __shfl_xor_sync(0xFFFFFFFFu, z, 2);
-      z |= __shfl_xor_sync(0xFFFFFFFFu, z, 4);
-      const unsigned long long h = finish_hash(a, l);
-      if (l == 0) {
-        uint32_t ts = kTsAbsent;
-        if (on) {
+    if (job == kJobAnalyze) {
+      uint4 ring[kRing];
+      uint64_t p = base + warp * 4 + g;
+      const uint4* src = image + p * 256 + l;
+      ring_fill<true>(ring, src, p < n_pages, keep_in_l2);
+#pragma unroll 1
+      for (int r = 0; r < kFusedRounds; r++) {
+        PageAcc a;
+        a.z = 0;
+        a.h = 0;
+        const bool on = p < n_pages;
+        const uint64_t p_next = p + kWarps * 4;
+        const uint4* src_next = image + p_next * 256 + l;
+        const bool next_on = (r + 1 < kFusedRounds) && p_next < n_pages;
+        page_pass<true, true, true>(a, ring, src, on, src_next, next_on, lane4, [](auto, const uint4&) {}, keep_in_l2);
+        const uint32_t page_crc = finish_crc(a, l);
+        uint32_t z = a.z;
+        z |= __shfl_xor_sync(0xFFFFFFFFu, z, 1);
+        z |= __shfl_xor_sync(0xFFFFFFFFu, z, 2);
+        z |= __shfl_xor_sync(0xFFFFFFFFu, z, 4);
+        const unsigned long long h = finish_hash(a, l);
+        if (l == 0 && on) {
           const uint64_t gp = page0 + p;
           crc[gp] = page_crc;
           hash[gp] = h;
-          ts = kTsZero;
+          uint32_t parked = 0u;  // zero page
           if (z) {
             const uint32_t v = kOriginSelf << 26 | (uint32_t)gp;
             uint64_t sl = table_home(h, t.mask);
@@ -566,40 +604,31 @@ k_pack_fused(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ image
                 break;
               }
             }
-            ts = (uint32_t)sl;
+            parked = 0x80000000u | (uint32_t)sl;  // the page's table slot, for the COPY job
           }
+          ref[gp] = parked;
         }
-        s_ts[grp][(uint32_t)(p - base)] = ts;
+        p = p_next;
+        src = src_next;
       }
-    });
-    __threadfence();  // crc/hash stores and table atomics before the group's flag
-    group_sync(grp);
-
-    // ---- B: ordering with earlier tiles, references, slots
-    if (gw == 0) {
-      if (lane == 0) st_status(&status[tile], kStInserted);
-      for (int64_t look = (int64_t)tile - 1; look >= 0; look -= 32) {
-        const int64_t idx = look - lane;
-        unsigned long long st;
-        do {
-          st = idx >= 0 ? ld_status(&status[idx]) : kStPrefix;
-        } while (__any_sync(0xFFFFFFFFu, (st >> 62) == 0));
-        if (__any_sync(0xFFFFFFFFu, (st >> 62) == 3)) break;  // everything below a PREFIX tile has inserted
-      }
-      __threadfence();
+      __threadfence();  // crc / hash / ref stores and table atomics before the flag
+      __syncthreads();
+      if (threadIdx.x == 0) st_status(&status[tile], kStInserted);
+      continue;
     }
-    group_sync(grp);
 
+    // ---- COPY(tile): every tile <= tile has inserted
+    __threadfence();
+    const uint32_t lp = threadIdx.x;
     uint32_t kind = 7u;  // 7 = no page
     bool keep = false;
-    uint64_t gp = 0;
-    if (gt < (uint32_t)kFusedTile) {
-      const uint32_t ts = s_ts[grp][gt];
-      gp = page0 + base + gt;
-      if (ts == kTsZero) {
+    uint64_t gp = page0 + base + lp;
+    if (lp < (uint32_t)kFusedTile && base + lp < n_pages) {
+      const uint32_t parked = ld_cg_u32(&ref[gp]);
+      if (parked == 0u) {
         kind = 0u;
-        ref[gp] = 0u;
-      } else if (ts != kTsAbsent) {
+      } else {
+        const uint32_t ts = parked & 0x7FFFFFFFu;
         const uint32_t v = ld_cg_u32(&t.vals[ts]), origin = v >> 26, idx = v & ((1u << 26) - 1);
         uint32_t out = kRefKeep;
         if (!(origin == kOriginSelf && idx == (uint32_t)gp)) {
@@ -616,19 +645,19 @@ k_pack_fused(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ image
         kind = keep ? 1u : out >> 29;
         if (!keep) ref[gp] = out;
       }
-      if (kind < 5u) n_kind[kind]++;
+      n_kind[kind]++;
     }
     const uint32_t bal = __ballot_sync(0xFFFFFFFFu, keep);
-    if (gw < (uint32_t)kTileWarps && lane == 0) s_warp_cnt[grp][gw] = __popc(bal);
-    group_sync(grp);
+    if (warp < 4 && lane == 0) s_warp_cnt[warp] = __popc(bal);
+    __syncthreads();
     uint32_t before = 0, total = 0;
 #pragma unroll
-    for (int w = 0; w < kTileWarps; w++) {
-      const uint32_t c = s_warp_cnt[grp][w];
-      before += w < (int)gw ? c : 0u;
+    for (int w = 0; w < 4; w++) {
+      const uint32_t c = s_warp_cnt[w];
+      before += w < (int)warp ? c : 0u;
       total += c;
     }
-    if (gw == 0) {
+    if (warp == 0) {
       if (lane == 0) st_status(&status[tile], (tile == 0 ? kStPrefix : kStAgg) | total);
       uint32_t excl = 0;
       if (tile > 0) {
@@ -651,7 +680,7 @@ k_pack_fused(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ image
         if (lane == 0) st_status(&status[tile], kStPrefix | (excl + total));
       }
       if (lane == 0) {
-        s_excl[grp] = excl;
+        s_excl = excl;
         if (tile == n_tiles - 1) {
           cnt->n_stored = excl + total;
           cnt->slot_base_next = ref_base + excl + total;
@@ -659,30 +688,36 @@ k_pack_fused(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ image
       }
     }
     const uint32_t rank = before + __popc(bal & ((1u << lane) - 1));
-    if (keep) s_list[grp][rank] = (uint16_t)gt;
-    group_sync(grp);
-    const uint64_t first_slot = out_base + s_excl[grp];
+    if (keep) s_list[rank] = (uint16_t)lp;
+    __syncthreads();
+    const uint64_t first_slot = out_base + s_excl;
     if (keep) {
-      ref[gp] = 1u << 29 | (uint32_t)(ref_base + s_excl[grp] + rank);
+      ref[gp] = 1u << 29 | (uint32_t)(ref_base + s_excl + rank);
       if (first_slot + rank >= capacity_pages) atomicAdd(&cnt->overflow, 1ull);
     }
-
-    // ---- C: copy the stored pages (L2 hits), one page per warp per step.  The ring already
-    // holds the next tile's first loads, which leaves room for one page in flight per warp.
-    for (uint32_t k = gw; k < total; k += kGroupWarps) {
-      const uint64_t sa = first_slot + k;
-      const uint4* pa = image + (base + s_list[grp][k]) * 256 + lane;
-      uint4 va[8];
+    for (uint32_t k = warp; k < total; k += 2 * kWarps) {
+      const uint32_t k2 = k + kWarps;
+      const bool two = k2 < total;
+      const uint64_t sa = first_slot + k, sb = first_slot + k2;
+      const uint4* pa = image + (base + s_list[k]) * 256 + lane;
+      const uint4* pb = image + (base + s_list[two ? k2 : k]) * 256 + lane;
+      uint4 va[8], vb[8];
 #pragma unroll
       for (int j = 0; j < 8; j++) va[j] = ldg_hint(pa + 32 * j, done_with);
+      if (two) {
+#pragma unroll
+        for (int j = 0; j < 8; j++) vb[j] = ldg_hint(pb + 32 * j, done_with);
+      }
       if (sa < capacity_pages) {
 #pragma unroll
         for (int j = 0; j < 8; j++) stg_hint(packed + sa * 256 + lane + 32 * j, va[j], done_with);
       }
+      if (two && sb < capacity_pages) {
+#pragma unroll
+        for (int j = 0; j < 8; j++) stg_hint(packed + sb * 256 + lane + 32 * j, vb[j], done_with);
+      }
     }
-    tile = next_tile;
-    // the barrier at the top of the next iteration separates these reads of s_list / s_excl / s_ts
-    // from the next tile's writes
+    __syncthreads();  // s_list / s_excl / s_warp_cnt are reused by the next COPY job
   }
 #pragma unroll
   for (int k = 0; k < 5; k++) {
@@ -838,7 +873,7 @@ cudaError_t launch_pack_fused(const LaunchGeom& g, const Gf2Tables* d_tab, const
                               PeerCrcs crcs, void* d_packed, uint64_t capacity_pages, uint64_t slot_base, bool chained,
                               unsigned long long* d_tile_status, DevCounters* d_cnt, cudaStream_t s) {
   if (!n_pages) return cudaSuccess;
-  const int grid = grid_for(g, n_pages, kFusedTile * kGroups, 1);
+  const int grid = grid_for(g, n_pages, kFusedTile, 1);
   k_pack_fused<<<grid, kThreads, kSmBytes, s>>>(d_tab, static_cast<const uint4*>(d_image), n_pages, page0, d_crc,
                                                 reinterpret_cast<unsigned long long*>(d_hash), d_ref, t, crcs,
                                                 static_cast<uint4*>(d_packed), capacity_pages, slot_base,

@@ -44,7 +44,9 @@ struct DevCounters {
   unsigned long long first_bad;  // restore: lowest such page
   unsigned long long slot_base;       // compact, chained mode: first slot of this launch
   unsigned long long slot_base_next;  // compact: slot_base + pages stored by this launch
-  unsigned int ticket;                // compact: dynamic tile counter
+  unsigned int ticket;                // compact / fused pack: next tile to analyse
+  unsigned int copy_ticket;           // fused pack: next tile whose pages are decided and copied
+  unsigned int watermark;             // fused pack: tiles [0, watermark) have entered their hashes in the table
   unsigned int pad;
 };
 

@@ -198,3 +198,37 @@ def test_calls_are_ordered_on_the_callers_stream(ctx, oracle):
             r = ctx.pack(big)
             out, rs = ctx.restore(r["packed"], r["ref"], r["crc"])
             assert rs["n_bad"] == 0 and torch.equal(out, big)
+
+
+def test_experimental_single_pass_pack_is_bit_exact_too():
+    """GRITPACK_FUSED=1 selects k_pack_fused (one pass over the image); it is opt-in because it is slower on B200
+    (profiles/README.md), but it must give the same bytes.  Runs in a fresh process: the switch is read once."""
+    import os
+    import subprocess
+    import sys
+    code = r'''
+import sys, numpy as np, torch
+sys.path.insert(0, "tests"); sys.path.insert(0, ".")
+import oracle_lib as O
+from grit_b200.buffers import Context
+ctx = Context(0)
+for n, kw in [(1, {}), (129, {}), (5000, {}), (3000, dict(pct_zero=40, pct_dup=55, dup_pool=3))]:
+    img = O.synth_image(n, 4242 + n, **kw)
+    g = ctx.pack(torch.from_numpy(img).cuda())
+    o = O.pack(img)
+    assert np.array_equal(g["ref"].cpu().numpy().view(np.uint32), o["ref"]), n
+    assert np.array_equal(g["crc"].cpu().numpy().view(np.uint32), o["crc"]), n
+    assert np.array_equal(g["packed"].cpu().numpy(), o["packed"]), n
+    assert {k: v for k, v in g["stats"].items() if k != "gpu_ms"} == o["stats"], n
+base = O.synth_image(2000, 9)
+pb = ctx.pack(torch.from_numpy(base).cuda())
+child = base.copy(); child[5 * 4096:6 * 4096] ^= 0xFF
+g = ctx.pack(torch.from_numpy(child).cuda(), parent=(pb["hash"], pb["crc"]))
+o = O.pack(child, parent=(pb["hash"].cpu().numpy().view(np.uint64), pb["crc"].cpu().numpy().view(np.uint32)))
+assert np.array_equal(g["ref"].cpu().numpy().view(np.uint32), o["ref"]) and g["stats"]["n_data"] == 1
+print("fused ok")
+'''
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", code], cwd=root, env=dict(os.environ, GRITPACK_FUSED="1"),
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "fused ok" in r.stdout, r.stdout + r.stderr
