@@ -216,6 +216,18 @@ int write_file(const std::string& path, const void* data, size_t len, std::strin
   return GRIT_OK;
 }
 
+// a manifest path must stay inside the destination: relative, no empty / "." / ".." component
+bool safe_relative(const std::string& p) {
+  if (p.empty() || p[0] == '/') return false;
+  for (size_t a = 0; a <= p.size();) {
+    const size_t b = std::min(p.find('/', a), p.size());
+    const std::string c = p.substr(a, b - a);
+    if (c.empty() || c == "." || c == "..") return false;
+    a = b + 1;
+  }
+  return true;
+}
+
 bool has_manifest(const std::string& dir) {
   struct stat st;
   return stat((dir + "/" + kManifest).c_str(), &st) == 0 && S_ISREG(st.st_mode);
@@ -248,8 +260,7 @@ int load_manifest(const std::string& dir, Manifest* m, std::string* msg) {
     e.size = r.get<uint64_t>();
     e.first_page = r.get<uint64_t>();
     e.path = r.str(r.get<uint32_t>());
-    if (e.path.empty() || e.path[0] == '/' || e.path.find("..") != std::string::npos)
-      return *msg = dir + ": manifest holds an unsafe path", GRIT_EFORMAT;
+    if (!safe_relative(e.path)) return *msg = dir + ": manifest holds an unsafe path", GRIT_EFORMAT;
     m->entries.push_back(std::move(e));
   }
   if (!r.ok || r.off + 4 != b.size() || m->n_pages > GRIT_MAX_PAGES) return *msg = dir + ": truncated manifest", GRIT_EFORMAT;

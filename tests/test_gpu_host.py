@@ -135,6 +135,7 @@ def test_empty_directory(tmp_path):
     src, pv, host = tmp_path / "src", tmp_path / "pv", tmp_path / "host"
     (src / "a" / "b").mkdir(parents=True)
     (src / "a" / "empty").write_bytes(b"")
+    (src / "a" / "we..ird name.img").write_bytes(b"dots and spaces are fine in a file name")
     copy.TransferData(str(src), str(pv), copy.UPLOAD)
     copy.TransferData(str(pv), str(host), copy.DOWNLOAD)
     assert tree_snapshot(str(host)) == tree_snapshot(str(src))
@@ -188,3 +189,21 @@ def test_config0_one_gib_criu_directory(oracle, tmp_path):
         assert tree_snapshot(host) == tree_snapshot(ref)
     finally:
         shutil.rmtree(root, ignore_errors=True)
+
+
+def test_cpp_grit_agent_binary(oracle, tmp_path):
+    """The C++ mirror of cmd/grit-agent (grit_b200/csrc/grit-agent): same flags, same messages, same result."""
+    import subprocess
+    exe = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "grit_b200", "csrc", "grit-agent")
+    src, pv, host = tmp_path / "src", tmp_path / "pv", tmp_path / "host"
+    src.mkdir()
+    make_criu_tree(str(src), oracle, big_pages=2000)
+    r = subprocess.run([exe, "--action", "checkpoint", "--src-dir", str(src), "--dst-dir", str(pv)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    r = subprocess.run([exe, "--action=restore", f"--src-dir={pv}", f"--dst-dir={host}"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert (host / "download-state").read_bytes() == b"Transfer Completed\n"
+    os.remove(host / "download-state")
+    assert tree_snapshot(str(host)) == tree_snapshot(str(src))
+    r = subprocess.run([exe, "--action", "migrate"], capture_output=True, text=True)
+    assert r.returncode == 1 and "run grit-agent failed: unknown action migrate" in r.stderr      # app.go:40,68
