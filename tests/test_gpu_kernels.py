@@ -232,3 +232,31 @@ print("fused ok")
     r = subprocess.run([sys.executable, "-c", code], cwd=root, env=dict(os.environ, GRITPACK_FUSED="1"),
                        capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and "fused ok" in r.stdout, r.stdout + r.stderr
+
+
+def test_dedup_rule_on_crafted_tables(ctx):
+    """K2 on hand-made (hash64, crc) arrays: the owner of a hash is the lowest (parent, peer rank, own page); a page
+    refers to it only when the CRC-32C matches too; a hash collision with another CRC is stored, never merged."""
+    PENDING, KEEP = 0xFFFFFFFF, 0xFFFFFFFE
+    i64, i32 = torch.int64, torch.int32
+
+    def arr(vals, dt):
+        return torch.tensor(vals, dtype=dt, device="cuda")
+    #        page:  0    1    2    3    4    5    6    7
+    h = arr([       11,  22,  11,  11,  33,  44,  55,  0], i64)
+    crc = arr([     1,   2,   1,   9,   3,   4,   5,   7], i32)     # page 3: hash of page 0, different CRC
+    ref = arr([PENDING] * 7 + [0], i64).to(i32)                    # page 7 is a zero page (never looked up)
+    parent = (arr([33, 44], i64), arr([3, 8], i32))                # hash 33 matches page 4 (CRC too); 44 collides (CRC differs)
+    peers = [(arr([55, 22], i64), arr([5, 2], i32)), (arr([55], i64), arr([5], i32))]
+    ctx.dedup(crc, h, ref, parent=parent, peers=peers)
+    got = [int(x) & 0xFFFFFFFF for x in ref.cpu().tolist()]
+    assert got == [
+        KEEP,                    # 0: first page with hash 11
+        4 << 29 | 0 << 26 | 1,   # 1: rank 0's page 1 holds hash 22 with the same CRC
+        2 << 29 | 0,             # 2: duplicate of page 0
+        KEEP,                    # 3: same hash64 as page 0 but another CRC: stored
+        3 << 29 | 0,             # 4: parent page 0
+        KEEP,                    # 5: parent holds hash 44 with another CRC: stored
+        4 << 29 | 0 << 26 | 0,   # 6: both peers hold it; the lowest rank owns it
+        0,                       # 7: zero page untouched
+    ]
