@@ -321,6 +321,45 @@ def run_gritpack(args):
                 "pack_whole": {"ms": round(t_pack, 4), "alg_bytes": n_bytes + U + 16 * n_pages,
                                "frac": round((n_bytes + U + 16 * n_pages) / (t_pack * 1e-3) / 1e9 / peak, 4)}}
 
+    # ---- the same kernels on the other page mixes of BASELINE.json (not the headline; parity-tested in tests/)
+    other = None
+    if world == 1 and not args.no_extra:
+        other = {}
+        full = ctx.pack(image, packed=packed, out=meta)
+        parent_tab = (full["hash"].clone(), full["crc"].clone())
+        # config 4: 5 % of the pages dirtied since the previous checkpoint, packed against its hash table
+        child = image.clone()
+        g = torch.Generator(device=dev).manual_seed(0xD1127)
+        dirty = torch.randperm(n_pages, device=dev, generator=g)[: n_pages // 20]
+        child.view(n_pages, PAGE)[dirty] = torch.randint(0, 256, (dirty.numel(), PAGE), dtype=torch.uint8, device=dev,
+                                                         generator=g)
+        ri = ctx.pack(child, parent=parent_tab, packed=packed)
+        t_p = timed(lambda: ctx.pack(child, parent=parent_tab, packed=packed))
+        t_r = timed(lambda: ctx.restore(ri["packed"], ri["ref"], ri["crc"], parent_image=image, out=restored))
+        assert torch.equal(restored, child), "incremental restore differs"
+        Ui = int(ri["stats"]["n_data"]) * PAGE
+        other["incremental_5pct_dirty"] = {
+            "page_mix": {k: int(v) for k, v in ri["stats"].items() if k.startswith("n_")},
+            "pack_ms": round(t_p, 3), "restore_ms": round(t_r, 3),
+            "pack_frac": round((n_bytes + Ui + 16 * n_pages) / (t_p * 1e-3) / 1e9 / peak, 4),
+            "restore_frac": round((n_bytes + n_bytes + 8 * n_pages) / (t_r * 1e-3) / 1e9 / peak, 4),
+            "note": "restore reads the unchanged pages from the parent image in HBM"}
+        del child
+        # config 1 mix: 10 % zero pages, 15 % duplicates from a 1024-page pool, 75 % unique
+        mix = ctx.synth_image(n_pages, seed=0xC0FFEE)
+        rm = ctx.pack(mix, packed=packed)
+        t_p = timed(lambda: ctx.pack(mix, packed=packed))
+        t_r = timed(lambda: ctx.restore(rm["packed"], rm["ref"], rm["crc"], out=restored))
+        assert torch.equal(restored, mix), "C1-mix restore differs"
+        Um = int(rm["stats"]["n_data"]) * PAGE
+        other["c1_mix_10zero_15dup"] = {
+            "page_mix": {k: int(v) for k, v in rm["stats"].items() if k.startswith("n_")},
+            "pack_ms": round(t_p, 3), "restore_ms": round(t_r, 3),
+            "pack_frac": round((n_bytes + Um + 16 * n_pages) / (t_p * 1e-3) / 1e9 / peak, 4),
+            "restore_frac": round((Um + n_bytes + 8 * n_pages) / (t_r * 1e-3) / 1e9 / peak, 4)}
+        del mix
+        torch.cuda.empty_cache()
+
     # ---- host link peaks of this box, measured now: the binding roofline of the e2e number
     def link_peaks(h_a, h_b, d_a, d_b):
         s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
@@ -412,7 +451,8 @@ def run_gritpack(args):
                        "page_mix": {k: int(v) for k, v in stats.items() if k.startswith("n_")}},
             "pack_gbs": round(world * n_bytes / (t_pack * 1e-3) / 1e9, 1),
             "restore_gbs": round(world * n_bytes / (t_restore * 1e-3) / 1e9, 1),
-            "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": int(launches),
+            "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "other_mixes": other,
+            "gpu_launches": int(launches),
             "clocks": clocks, "bit_exact": True,
         }
         print(json.dumps(line))
@@ -430,6 +470,7 @@ def main():
     ap.add_argument("--pages", type=int, default=0, help="override pages per GPU (debug only; invalid as a bench number)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the other page mixes")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
