@@ -228,7 +228,7 @@ def run_gritpack(args):
             return ctx.pack(image, packed=packed, out=meta)
         from grit_b200 import dist as gdist
         crc, h, ref = ctx.analyze(image)
-        tables = gdist.all_gather_tables(h, crc)          # NCCL over NVLink: 12 B per 4 KiB page
+        tables = gdist.all_gather_tables(h, crc, counts=[n_pages] * world)   # NCCL over NVLink: 12 B per 4 KiB page
         ctx.dedup(crc, h, ref, peers=gdist.peers_of(rank, tables))
         n = ctx.compact(image, ref, packed)
         return dict(ref=ref, crc=crc, hash=h, packed=packed[: n * PAGE], stats={"n_data": n})

@@ -116,39 +116,55 @@ int dedup_async(grit_ctx* ctx, uint64_t n_pages, const uint32_t* d_crc, const ui
                 const grit_table* parent, const grit_table* peers, uint32_t n_peers, cudaStream_t s, char* err,
                 size_t errlen, DedupTable* table_out = nullptr, PeerCrcs* crcs_out = nullptr) {
   if (n_peers > GRIT_MAX_PEERS) return fail(err, errlen, GRIT_EINVAL, "n_peers %u > %u", n_peers, GRIT_MAX_PEERS);
-  uint64_t items = n_pages;
   PeerCrcs crcs{};
-  if (parent && parent->n_pages) {
+  uint64_t items = n_pages;
+  const bool parent_on = parent && parent->n_pages;
+  if (parent_on) {
     if (parent->n_pages > GRIT_MAX_PAGES) return fail(err, errlen, GRIT_EINVAL, "parent too large");
-    items += parent->n_pages;
     crcs.parent = parent->crc;
   }
   for (uint32_t r = 0; r < n_peers; r++) {
     if (peers[r].n_pages > GRIT_MAX_PAGES) return fail(err, errlen, GRIT_EINVAL, "peer too large");
-    items += peers[r].n_pages;
     crcs.peer[r] = peers[r].crc;
+  }
+  // The fused kernel inserts this image's pages itself, after the others: its table must hold them all.
+  // The staged path inserts this image first and only probes with the others, so the table is sized by
+  // this image alone whatever the number of peers.
+  if (table_out) {
+    if (parent_on) items += parent->n_pages;
+    for (uint32_t r = 0; r < n_peers; r++) items += peers[r].n_pages;
   }
   DedupTable t{};
   if (int rc = ensure_table(ctx, items, &t, err, errlen)) return rc;
   GRIT_CUDA(cudaMemsetAsync(t.keys, 0, (t.mask + 1) * sizeof(unsigned long long), s));
   GRIT_CUDA(cudaMemsetAsync(t.vals, 0xFF, (t.mask + 1) * sizeof(uint32_t), s));
-  if (parent && parent->n_pages) {
-    GRIT_CUDA(launch_table_insert(ctx->geom, t, parent->hash, nullptr, parent->n_pages, 0, 0, s));
-    ctx->launches++;
-  }
-  for (uint32_t r = 0; r < n_peers; r++)
-    if (peers[r].n_pages) {
-      GRIT_CUDA(launch_table_insert(ctx->geom, t, peers[r].hash, nullptr, peers[r].n_pages, 1 + r, 0, s));
+  if (table_out) {
+    if (parent_on) {
+      GRIT_CUDA(launch_table_insert(ctx->geom, t, parent->hash, nullptr, parent->n_pages, 0, 0, s));
       ctx->launches++;
     }
-  if (table_out) {  // the fused kernel inserts and resolves this image's own pages itself
+    for (uint32_t r = 0; r < n_peers; r++)
+      if (peers[r].n_pages) {
+        GRIT_CUDA(launch_table_insert(ctx->geom, t, peers[r].hash, nullptr, peers[r].n_pages, 1 + r, 0, s));
+        ctx->launches++;
+      }
     *table_out = t;
     *crcs_out = crcs;
     return GRIT_OK;
   }
   GRIT_CUDA(launch_table_insert(ctx->geom, t, d_hash, d_ref, n_pages, kOriginSelf, 0, s));
+  ctx->launches++;
+  if (parent_on) {
+    GRIT_CUDA(launch_table_probe(ctx->geom, t, parent->hash, parent->n_pages, 0, s));
+    ctx->launches++;
+  }
+  for (uint32_t r = 0; r < n_peers; r++)
+    if (peers[r].n_pages) {
+      GRIT_CUDA(launch_table_probe(ctx->geom, t, peers[r].hash, peers[r].n_pages, 1 + r, s));
+      ctx->launches++;
+    }
   GRIT_CUDA(launch_resolve(ctx->geom, t, 0, n_pages, d_crc, d_hash, d_ref, crcs, s));
-  ctx->launches += 2;
+  ctx->launches++;
   return GRIT_OK;
 }
 

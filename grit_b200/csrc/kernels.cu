@@ -313,6 +313,24 @@ k_table_insert(DedupTable t, const unsigned long long* __restrict__ hash, const 
   }
 }
 
+// Other images' hashes against a table that already holds this image's: a hit lowers the owner,
+// a miss touches nothing, so the table stays the size of this image however many peers there are.
+__global__ void __launch_bounds__(256)
+k_table_probe(DedupTable t, const unsigned long long* __restrict__ hash, uint64_t n, uint32_t origin) {
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (uint64_t)gridDim.x * blockDim.x) {
+    const unsigned long long h = hash[i];
+    for (uint64_t s = table_home(h, t.mask);; s = (s + 1) & t.mask) {
+      const unsigned long long k = t.keys[s];
+      if (k == h) {
+        atomicMin(&t.vals[s], origin << 26 | (uint32_t)i);
+        break;
+      }
+      if (k == 0ull) break;
+    }
+  }
+}
+
 __global__ void __launch_bounds__(256)
 k_resolve(DedupTable t, uint64_t page0, uint64_t page1, const uint32_t* __restrict__ crc,
           const unsigned long long* __restrict__ hash, uint32_t* __restrict__ ref, PeerCrcs crcs) {
@@ -896,6 +914,13 @@ cudaError_t launch_table_insert(const LaunchGeom& g, DedupTable t, const uint64_
   if (!n) return cudaSuccess;
   k_table_insert<<<grid_for(g, n, 256, 8), 256, 0, s>>>(
       t, reinterpret_cast<const unsigned long long*>(d_hash), d_ref_or_null, n, origin, index_base);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_table_probe(const LaunchGeom& g, DedupTable t, const uint64_t* d_hash, uint64_t n, uint32_t origin,
+                               cudaStream_t s) {
+  if (!n) return cudaSuccess;
+  k_table_probe<<<grid_for(g, n, 256, 8), 256, 0, s>>>(t, reinterpret_cast<const unsigned long long*>(d_hash), n, origin);
   return cudaGetLastError();
 }
 

@@ -10,18 +10,21 @@ import torch
 import torch.distributed as dist
 
 
-def all_gather_tables(h, crc, group=None):
+def all_gather_tables(h, crc, group=None, counts=None):
     """h: int64[n_pages], crc: int32[n_pages] of this rank (any device the backend supports).
 
-    Ranks may hold different page counts: counts are gathered first and the arrays padded to the maximum.
+    Ranks may hold different page counts: counts are gathered first and the arrays padded to the maximum
+    (pass `counts`, the page count of every rank, when they are known, to skip that exchange and its host sync).
     Returns [(hash_r, crc_r) for r in range(world)], each trimmed to rank r's own page count.
     """
     world = dist.get_world_size(group)
-    n = torch.tensor([h.numel()], dtype=torch.int64, device=h.device)
-    counts = [torch.zeros_like(n) for _ in range(world)]
-    dist.all_gather(counts, n, group=group)
-    counts = [int(c.item()) for c in counts]
-    m = max(counts + [1])
+    if counts is None:
+        n = torch.tensor([h.numel()], dtype=torch.int64, device=h.device)
+        gathered = [torch.zeros_like(n) for _ in range(world)]
+        dist.all_gather(gathered, n, group=group)
+        counts = [int(c.item()) for c in gathered]
+    assert len(counts) == world and counts[dist.get_rank(group)] == h.numel()
+    m = max(list(counts) + [1])
 
     def padded(t):
         if t.numel() == m:
