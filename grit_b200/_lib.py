@@ -28,10 +28,12 @@ class Table(C.Structure):
 
 class PackStats(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ("n_pages", "n_zero", "n_data", "n_dup", "n_parent", "n_peer")] + [
-        ("gpu_ms", C.c_double)]
+        ("gpu_ms", C.c_double), ("stage_ms", C.c_double * 3), ("wrote_through", C.c_uint64)]
 
     def as_dict(self):
-        return {n: getattr(self, n) for n, _ in self._fields_}
+        d = {n: getattr(self, n) for n, _ in self._fields_ if n != "stage_ms"}
+        d["stage_ms"] = [float(x) for x in self.stage_ms]
+        return d
 
 
 class RestoreStats(C.Structure):

@@ -44,7 +44,8 @@ int ensure_status(grit_ctx* ctx, uint64_t n_pages, char* err, size_t errlen) {
 
 int reset_counters(grit_ctx* ctx, cudaStream_t s, char* err, size_t errlen) {
   GRIT_CUDA(cudaMemsetAsync(ctx->d_cnt, 0, sizeof(DevCounters), s));
-  GRIT_CUDA(cudaMemsetAsync(&ctx->d_cnt->first_bad, 0xFF, sizeof(unsigned long long), s));
+  GRIT_CUDA(cudaMemsetAsync(&ctx->d_cnt->first_bad, 0xFF, 2 * sizeof(unsigned long long), s));  // first_bad, first_drop
+  GRIT_CUDA(cudaMemsetAsync(&ctx->d_cnt->dense_hint, 1, 1, s));  // little endian: dense_hint = 1
   return GRIT_OK;
 }
 
@@ -52,6 +53,15 @@ int read_counters(grit_ctx* ctx, cudaStream_t s, char* err, size_t errlen) {
   GRIT_CUDA(cudaMemcpyAsync(ctx->h_cnt, ctx->d_cnt, sizeof(DevCounters), cudaMemcpyDeviceToHost, s));
   GRIT_CUDA(cudaStreamSynchronize(s));
   return GRIT_OK;
+}
+
+// GRITPACK_WRITE_THROUGH=0 turns the write-through K1 off (A/B measurements).
+bool write_through_pack() {
+  static const bool v = [] {
+    const char* e = getenv("GRITPACK_WRITE_THROUGH");
+    return !(e && *e == '0');
+  }();
+  return v;
 }
 
 // The pack runs K1, K2, K3 as three kernels (DRAM traffic N + 2U).  GRITPACK_FUSED=1 selects the
@@ -169,12 +179,13 @@ int dedup_async(grit_ctx* ctx, uint64_t n_pages, const uint32_t* d_crc, const ui
 }
 
 int compact_async(grit_ctx* ctx, const void* d_image, uint64_t n_pages, uint32_t* d_ref, void* d_packed,
-                  uint64_t capacity_pages, uint64_t slot_base, cudaStream_t s, char* err, size_t errlen) {
+                  uint64_t capacity_pages, uint64_t slot_base, cudaStream_t s, char* err, size_t errlen,
+                  bool in_place = false) {
   if (int rc = ensure_status(ctx, n_pages, err, errlen)) return rc;
   const uint64_t tiles = (n_pages + kCompactTile - 1) / kCompactTile;
   GRIT_CUDA(cudaMemsetAsync(ctx->d_status, 0, tiles * sizeof(unsigned long long), s));
   GRIT_CUDA(launch_compact(ctx->geom, d_image, n_pages, d_ref, d_packed, capacity_pages, slot_base, false, ctx->d_status,
-                           ctx->d_cnt, s));
+                           ctx->d_cnt, s, in_place));
   ctx->launches++;
   return GRIT_OK;
 }
@@ -218,6 +229,8 @@ int grit_ctx_create(int device, grit_ctx** out, char* err, size_t errlen) {
   CTX_CUDA(cudaStreamCreateWithFlags(&ctx->d2h, cudaStreamNonBlocking));
   CTX_CUDA(cudaEventCreate(&ctx->ev0));
   CTX_CUDA(cudaEventCreate(&ctx->ev1));
+  CTX_CUDA(cudaEventCreate(&ctx->evA));
+  CTX_CUDA(cudaEventCreate(&ctx->evB));
   CTX_CUDA(cudaMalloc(&ctx->d_tables, sizeof(Gf2Tables)));
   CTX_CUDA(cudaMalloc(&ctx->d_cnt, sizeof(DevCounters)));
   CTX_CUDA(cudaMallocHost(&ctx->h_cnt, sizeof(DevCounters)));
@@ -251,6 +264,8 @@ void grit_ctx_destroy(grit_ctx* ctx) {
   if (ctx->h_cnt) cudaFreeHost(ctx->h_cnt);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+  if (ctx->evA) cudaEventDestroy(ctx->evA);
+  if (ctx->evB) cudaEventDestroy(ctx->evB);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   if (ctx->h2d) cudaStreamDestroy(ctx->h2d);
   if (ctx->d2h) cudaStreamDestroy(ctx->d2h);
@@ -311,11 +326,25 @@ int grit_pack_buffer(grit_ctx* ctx, const void* d_image, uint64_t n_pages, const
   cudaStream_t s = pick(ctx, stream);
   if (int rc = reset_counters(ctx, s, err, errlen)) return rc;
   GRIT_CUDA(cudaEventRecord(ctx->ev0, s));
+  bool staged = false;
   if (staged_pack()) {  // K1, K2, K3 as separate kernels
-    GRIT_CUDA(launch_analyze(ctx->geom, ctx->d_tables, d_image, n_pages, d_crc, d_hash, d_ref, s));
-    ctx->launches++;
+    // A full (not incremental, single-rank) image may be dense -- weights, optimizer state: no zero pages,
+    // no duplicates -- and then compaction is the identity: K1 writes such pages through to their own
+    // slot and K3 finds them in place.  A sample of the image decides, on the device.
+    const bool try_through = !(parent && parent->n_pages) && n_peers == 0 && d_packed && write_through_pack();
+    if (try_through) {
+      GRIT_CUDA(launch_analyze_auto(ctx->geom, ctx->d_tables, d_image, n_pages, d_crc, d_hash, d_ref, d_packed,
+                                    capacity_pages, ctx->d_cnt, s));
+      ctx->launches += 3;
+    } else {
+      GRIT_CUDA(launch_analyze(ctx->geom, ctx->d_tables, d_image, n_pages, d_crc, d_hash, d_ref, s));
+      ctx->launches++;
+    }
+    GRIT_CUDA(cudaEventRecord(ctx->evA, s));
     if (int rc = dedup_async(ctx, n_pages, d_crc, d_hash, d_ref, parent, peers, n_peers, s, err, errlen)) return rc;
-    if (int rc = compact_async(ctx, d_image, n_pages, d_ref, d_packed, capacity_pages, 0, s, err, errlen)) return rc;
+    GRIT_CUDA(cudaEventRecord(ctx->evB, s));
+    staged = true;
+    if (int rc = compact_async(ctx, d_image, n_pages, d_ref, d_packed, capacity_pages, 0, s, err, errlen, try_through)) return rc;
   } else if (n_pages) {
     DedupTable t{};
     PeerCrcs crcs{};
@@ -340,6 +369,17 @@ int grit_pack_buffer(grit_ctx* ctx, const void* d_image, uint64_t n_pages, const
     float ms = 0;
     cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
     stats->gpu_ms = ms;
+    stats->stage_ms[0] = stats->stage_ms[1] = stats->stage_ms[2] = 0;
+    if (staged && n_pages) {
+      cudaEventElapsedTime(&ms, ctx->ev0, ctx->evA);
+      stats->stage_ms[0] = ms;
+      cudaEventElapsedTime(&ms, ctx->evA, ctx->evB);
+      stats->stage_ms[1] = ms;
+      cudaEventElapsedTime(&ms, ctx->evB, ctx->ev1);
+      stats->stage_ms[2] = ms;
+    }
+    stats->wrote_through = staged && n_pages && !(parent && parent->n_pages) && n_peers == 0 && d_packed &&
+                           write_through_pack() && c.dense_hint;
   }
   if (c.overflow)
     return fail(err, errlen, GRIT_EINVAL, "packed buffer too small: %llu pages did not fit capacity %llu",

@@ -16,7 +16,7 @@ struct grit_ctx {
   cudaStream_t stream = nullptr;  // kernels
   cudaStream_t h2d = nullptr;     // host pipeline copy-in
   cudaStream_t d2h = nullptr;     // host pipeline copy-out
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, evA = nullptr, evB = nullptr;
   grit::Gf2Tables* d_tables = nullptr;
   grit::DevCounters* d_cnt = nullptr;
   grit::DevCounters* h_cnt = nullptr;  // pinned mirror
@@ -68,6 +68,7 @@ int ctx_pin(grit_ctx* ctx, int id, size_t bytes, void** out, char* err, size_t e
 enum DevBuf { kDevIn0 = 0, kDevOut0 = 3, kDevRef = 6, kDevCrc, kDevHash, kDevParentHash, kDevParentCrc,
               kDevRPacked, kDevRRef, kDevRCrc, kDevROut0 = 14, kDevRParent = 17 };
 enum PinBuf { kPinIn0 = 0, kPinOut0 = 3, kPinCounts = 6, kPinMeta0 = 7, kPinRStageOut0 = 10, kPinRStageIn0 = 13 /* ..15 */ };
+bool write_through_pack();  // false with GRITPACK_WRITE_THROUGH=0
 bool staged_pack();  // true unless GRITPACK_FUSED=1 selects the experimental single-pass pack kernel
 
 }  // namespace grit

@@ -221,6 +221,8 @@ int PackStream::finish(grit_pack_stats* stats, char* err, size_t errlen) {
     float ms = 0;
     if (timing_started_) cudaEventElapsedTime(&ms, ctx_->ev0, ctx_->ev1);
     stats->gpu_ms = ms;
+    stats->stage_ms[0] = stats->stage_ms[1] = stats->stage_ms[2] = 0;
+    stats->wrote_through = 0;
   }
   if (c.overflow) return fail(err, errlen, GRIT_EINVAL, "internal: chunk output overflow");
   return GRIT_OK;

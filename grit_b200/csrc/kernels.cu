@@ -250,7 +250,9 @@ __device__ __forceinline__ unsigned long long finish_hash(const PageAcc& a, uint
 // A warp takes four consecutive pages per step; lanes 8g..8g+7 own page g.
 __global__ void __launch_bounds__(kThreads, 1)
 k_analyze(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ image, uint64_t n_pages,
-          uint32_t* __restrict__ crc, unsigned long long* __restrict__ hash, uint32_t* __restrict__ ref) {
+          uint32_t* __restrict__ crc, unsigned long long* __restrict__ hash, uint32_t* __restrict__ ref,
+          const DevCounters* __restrict__ cnt, int want_hint) {
+  if (want_hint >= 0 && (int)cnt->dense_hint != want_hint) return;  // the write-through variant runs instead
   load_tables(tabs);
   const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const uint32_t g = lane >> 3, l = lane & 7, lane4 = lane * 4;
@@ -287,6 +289,122 @@ k_analyze(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ image, u
     p = p_next;
     src = src_next;
   }
+}
+
+// ------------------------------------------------------------------ K1 with write-through
+// For images that need (almost) no compaction -- model weights and optimizer state have no zero
+// pages and no duplicates, so slot(p) == p for every page up to the first page that is dropped --
+// every page is stored to packed[p] while it is analysed, and K3 finds those pages in place and
+// only moves what lies behind the first dropped page: N read + N written of DRAM traffic, the
+// algorithmic minimum, instead of N + 2N.
+// CRC + hash64 + a register load ring + stores do not fit 128 registers, so here the load ring
+// lives in shared memory: each lane's 16-byte loads are cp.async copies (global -> shared, no
+// register) into a private slot that the same lane reads back with one LDS.128 seven steps later.
+constexpr int kSmRing = 7;                       // cp.async copies each lane keeps in flight
+constexpr uint32_t kSmRingBase = kSmBytes;       // behind the tables
+constexpr uint32_t kSmBytesWT = kSmBytes + kSmRing * kThreads * 16;  // 225 280 B of the 232 448 B limit
+
+__device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void* gptr) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(gptr) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ uint4 lds128(uint32_t smem_addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(smem_addr) : "memory");
+  return v;
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+k_analyze_through(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ image, uint64_t n_pages,
+                  uint32_t* __restrict__ crc, unsigned long long* __restrict__ hash, uint32_t* __restrict__ ref,
+                  uint4* __restrict__ packed, uint64_t capacity_pages, DevCounters* __restrict__ cnt, int want_hint) {
+  if (want_hint >= 0 && (int)cnt->dense_hint != want_hint) return;  // the other K1 variant runs instead
+  load_tables(tabs);
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t g = lane >> 3, l = lane & 7, lane4 = lane * 4;
+  const uint64_t n_groups = (n_pages + 3) / 4;
+  const uint64_t stride = (uint64_t)gridDim.x * kWarps;
+  uint64_t grp = (uint64_t)blockIdx.x * kWarps + warp;
+  if (grp >= n_groups) return;
+  const uint32_t ring0 = (uint32_t)__cvta_generic_to_shared(smem) + kSmRingBase + threadIdx.x * 16;  // slot s at + s * 8192
+  const uint64_t last = n_pages - 1;
+
+  // every step issues exactly one copy and one commit, so "at most kSmRing-1 groups pending" always
+  // means that the oldest slot has landed; pages past the end re-read the last page (result dropped)
+  uint64_t p = 4 * grp + g;
+  const uint4* src = image + (p < last ? p : last) * 256 + l;
+#pragma unroll
+  for (int j = 0; j < kSmRing; j++) {
+    cp_async16(ring0 + j * (kThreads * 16), src + 8 * j);
+    cp_async_commit();
+  }
+  uint32_t slot = 0;
+  for (; grp < n_groups; grp += stride) {
+    PageAcc a;
+    a.z = 0;
+    a.h = 0;
+    const bool on = p < n_pages;
+    const unsigned long long first_drop = __ldcg(&cnt->first_drop);
+    const bool through = on && p < capacity_pages && p < first_drop;
+    uint4* d = packed + p * 256 + l;
+    const uint64_t p_next = 4 * (grp + stride) + g;
+    const uint64_t p_load = grp + stride < n_groups ? (p_next < last ? p_next : last) : (p < last ? p : last);
+    const uint4* src_next = image + p_load * 256 + l;
+    static_for<0, 32>([&](auto jc) {
+      constexpr int j = decltype(jc)::value;
+      cp_async_wait<kSmRing - 1>();
+      const uint32_t sa = ring0 + slot * (kThreads * 16);
+      const uint4 v = lds128(sa);
+      if (through) stg_stream(d + 8 * j, v);
+      cp_async16(sa, j + kSmRing < 32 ? src + 8 * (j + kSmRing) : src_next + 8 * (j + kSmRing - 32));
+      cp_async_commit();
+      slot = slot + 1 == kSmRing ? 0 : slot + 1;
+      if (j % 8 == 0 && j > 0) a.h *= kGold;
+      absorb<j % 8, j == 0, true>(a, v, lane4);
+    });
+    const uint32_t page_crc = finish_crc(a, l);
+    uint32_t z = a.z;
+    z |= __shfl_xor_sync(0xFFFFFFFFu, z, 1);
+    z |= __shfl_xor_sync(0xFFFFFFFFu, z, 2);
+    z |= __shfl_xor_sync(0xFFFFFFFFu, z, 4);
+    const unsigned long long page_hash = finish_hash(a, l);
+    if (l == 0 && on) {
+      crc[p] = page_crc;
+      hash[p] = page_hash;
+      ref[p] = z ? kRefPending : 0u;
+      if (!z && p < first_drop) atomicMin(&cnt->first_drop, (unsigned long long)p);
+    }
+    p = p_next;
+    src = src_next;
+  }
+  cp_async_wait<0>();
+}
+
+// Looks at 4096 evenly spread pages (128 bytes of each): any that reads as zero means the image is not
+// dense and plain K1 + K3 is the cheaper pack.  Sets cnt->dense_hint for the two K1 variants and K3.
+__global__ void __launch_bounds__(256)
+k_probe_dense(const uint4* __restrict__ image, uint64_t n_pages, DevCounters* __restrict__ cnt) {
+  __shared__ int s_zero;
+  if (threadIdx.x == 0) s_zero = 0;
+  __syncthreads();
+  const uint32_t n_samples = 4096;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_samples; i += gridDim.x * blockDim.x) {
+    const uint64_t p = (uint64_t)i * n_pages / n_samples;
+    const uint4* q = image + p * 256;
+    uint32_t o = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      const uint4 v = __ldg(q + 32 * k + (i & 31));
+      o |= v.x | v.y | v.z | v.w;
+    }
+    if (o == 0) s_zero = 1;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0 && s_zero) atomicExch(&cnt->dense_hint, 0u);
 }
 
 // ------------------------------------------------------------------ K2 dedup
@@ -373,9 +491,10 @@ __device__ __forceinline__ void st_status(unsigned long long* p, unsigned long l
 
 __global__ void __launch_bounds__(256)
 k_compact(const uint4* __restrict__ image, uint64_t n_pages, uint32_t* __restrict__ ref,
-          uint4* __restrict__ packed, uint64_t capacity_pages, uint64_t slot_base, int chained,
+          uint4* __restrict__ packed, uint64_t capacity_pages, uint64_t slot_base, int chained, int in_place,
           unsigned long long* __restrict__ status, DevCounters* __restrict__ cnt) {
   __shared__ uint32_t s_tile, s_warp_cnt[8], s_excl;
+  in_place = in_place && cnt->dense_hint;  // the write-through K1 ran: pages in front of the first drop are in place
   __shared__ uint16_t s_list[kCompactTile];
   const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const uint32_t n_tiles = (uint32_t)((n_pages + kCompactTile - 1) / kCompactTile);
@@ -455,8 +574,12 @@ k_compact(const uint4* __restrict__ image, uint64_t n_pages, uint32_t* __restric
       ref[p] = 1u << 29 | (uint32_t)(ref_base + s_excl + rank);
       if (first_slot + rank >= capacity_pages) atomicAdd(&cnt->overflow, 1ull);
     }
+    // after a write-through K1 a tile whose pages all keep their own index is already in place
+    const uint64_t tile_base = (uint64_t)tile * kCompactTile;
+    const uint32_t tile_pages = (uint32_t)(n_pages - tile_base < kCompactTile ? n_pages - tile_base : kCompactTile);
+    const bool tile_in_place = in_place && first_slot == tile_base && total == tile_pages;
     // copy: one page per warp per step, two steps in flight
-    for (uint32_t k = warp; k < total; k += 16) {
+    for (uint32_t k = tile_in_place ? total : warp; k < total; k += 16) {
       const uint32_t k2 = k + 8;
       const bool two = k2 < total;
       const uint64_t sa = first_slot + k, sb = first_slot + k2;
@@ -879,6 +1002,8 @@ uint32_t page_kernel_smem_bytes() { return kSmBytes; }
 cudaError_t configure_kernels() {
   cudaError_t e = cudaFuncSetAttribute(k_analyze, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmBytes);
   if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(k_analyze_through, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmBytesWT);
+  if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(k_pack_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmBytes);
   if (e != cudaSuccess) return e;
   return cudaFuncSetAttribute(k_restore, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmBytes);
@@ -904,7 +1029,24 @@ cudaError_t launch_analyze(const LaunchGeom& g, const Gf2Tables* d_tab, const vo
   if (!n_pages) return cudaSuccess;
   const int grid = grid_for(g, (n_pages + 3) / 4, kWarps, 1);
   k_analyze<<<grid, kThreads, kSmBytes, s>>>(d_tab, static_cast<const uint4*>(d_image), n_pages, d_crc,
-                                             reinterpret_cast<unsigned long long*>(d_hash), d_ref);
+                                             reinterpret_cast<unsigned long long*>(d_hash), d_ref, nullptr, -1);
+  return cudaGetLastError();
+}
+
+// K1 for a full, single-rank image: samples the image, then runs the write-through variant if it looks
+// dense (no zero page among the samples) and plain K1 otherwise -- decided on the device, no host sync.
+// d_cnt->dense_hint must be 1 on entry (reset_counters does that); K3 reads it to skip pages in place.
+cudaError_t launch_analyze_auto(const LaunchGeom& g, const Gf2Tables* d_tab, const void* d_image, uint64_t n_pages,
+                                uint32_t* d_crc, uint64_t* d_hash, uint32_t* d_ref, void* d_packed,
+                                uint64_t capacity_pages, DevCounters* d_cnt, cudaStream_t s) {
+  if (!n_pages) return cudaSuccess;
+  const int grid = grid_for(g, (n_pages + 3) / 4, kWarps, 1);
+  k_probe_dense<<<16, 256, 0, s>>>(static_cast<const uint4*>(d_image), n_pages, d_cnt);
+  k_analyze_through<<<grid, kThreads, kSmBytesWT, s>>>(d_tab, static_cast<const uint4*>(d_image), n_pages, d_crc,
+                                                       reinterpret_cast<unsigned long long*>(d_hash), d_ref,
+                                                       static_cast<uint4*>(d_packed), capacity_pages, d_cnt, 1);
+  k_analyze<<<grid, kThreads, kSmBytes, s>>>(d_tab, static_cast<const uint4*>(d_image), n_pages, d_crc,
+                                             reinterpret_cast<unsigned long long*>(d_hash), d_ref, d_cnt, 0);
   return cudaGetLastError();
 }
 
@@ -934,11 +1076,11 @@ cudaError_t launch_resolve(const LaunchGeom& g, DedupTable t, uint64_t page0, ui
 
 cudaError_t launch_compact(const LaunchGeom& g, const void* d_image, uint64_t n_pages, uint32_t* d_ref,
                            void* d_packed, uint64_t capacity_pages, uint64_t slot_base, bool chained,
-                           unsigned long long* d_tile_status, DevCounters* d_cnt, cudaStream_t s) {
+                           unsigned long long* d_tile_status, DevCounters* d_cnt, cudaStream_t s, bool in_place) {
   if (!n_pages) return cudaSuccess;
   k_compact<<<grid_for(g, n_pages, kCompactTile, 8), 256, 0, s>>>(
       static_cast<const uint4*>(d_image), n_pages, d_ref, static_cast<uint4*>(d_packed), capacity_pages,
-      slot_base, chained ? 1 : 0, d_tile_status, d_cnt);
+      slot_base, chained ? 1 : 0, (in_place && !chained && slot_base == 0) ? 1 : 0, d_tile_status, d_cnt);
   return cudaGetLastError();
 }
 

@@ -42,12 +42,13 @@ struct DevCounters {
   unsigned long long overflow;   // pages that did not fit capacity_pages
   unsigned long long n_bad;      // restore: pages that failed
   unsigned long long first_bad;  // restore: lowest such page
+  unsigned long long first_drop;      // write-through K1: lowest zero page seen so far (UINT64_MAX: none)
   unsigned long long slot_base;       // compact, chained mode: first slot of this launch
   unsigned long long slot_base_next;  // compact: slot_base + pages stored by this launch
   unsigned int ticket;                // compact / fused pack: next tile to analyse
   unsigned int copy_ticket;           // fused pack: next tile whose pages are decided and copied
   unsigned int watermark;             // fused pack: tiles [0, watermark) have entered their hashes in the table
-  unsigned int pad;
+  unsigned int dense_hint;            // 1: the sampled pages held no zero page, K1 writes through
 };
 
 struct LaunchGeom {
@@ -66,7 +67,12 @@ cudaError_t launch_resolve(const LaunchGeom& g, DedupTable t, uint64_t page0, ui
                            const uint64_t* d_hash, uint32_t* d_ref, PeerCrcs crcs, cudaStream_t s);
 cudaError_t launch_compact(const LaunchGeom& g, const void* d_image, uint64_t n_pages, uint32_t* d_ref,
                            void* d_packed, uint64_t capacity_pages, uint64_t slot_base, bool chained,
-                           unsigned long long* d_tile_status, DevCounters* d_cnt, cudaStream_t s);
+                           unsigned long long* d_tile_status, DevCounters* d_cnt, cudaStream_t s,
+                           bool in_place = false);
+// K1 for a full single-rank image: write-through variant when the image looks dense, plain K1 otherwise
+cudaError_t launch_analyze_auto(const LaunchGeom& g, const Gf2Tables* d_tab, const void* d_image, uint64_t n_pages,
+                                uint32_t* d_crc, uint64_t* d_hash, uint32_t* d_ref, void* d_packed,
+                                uint64_t capacity_pages, DevCounters* d_cnt, cudaStream_t s);
 // K1+K2+K3 in one pass; crc/hash/ref are the whole image's arrays, the chunk starts at page0 of them
 cudaError_t launch_pack_fused(const LaunchGeom& g, const Gf2Tables* d_tab, const void* d_image, uint64_t n_pages,
                               uint64_t page0, uint32_t* d_crc, uint64_t* d_hash, uint32_t* d_ref, DedupTable t,

@@ -62,7 +62,9 @@ typedef struct grit_table {
 
 typedef struct grit_pack_stats {
   uint64_t n_pages, n_zero, n_data, n_dup, n_parent, n_peer;
-  double gpu_ms; /* device time of the kernels of this call (CUDA events) */
+  double gpu_ms;      /* device time of the kernels of this call (CUDA events) */
+  double stage_ms[3]; /* grit_pack_buffer: K1, K2, K3 separately (0 elsewhere)  */
+  uint64_t wrote_through; /* 1: K1 stored the pages to their own slots (dense image) */
 } grit_pack_stats;
 
 typedef struct grit_restore_stats {
@@ -166,7 +168,13 @@ int grit_compact_pages_static(int device, const void *d_image, uint64_t n_pages,
                               uint64_t *n_stored, void *stream, char *err,
                               size_t errlen);
 
-/* K1+K2+K3 on one device-resident image; the unit bench.py times as `value`. */
+/* K1+K2+K3 on one device-resident image; the unit bench.py times as `value`.
+ * For a full image (no parent, no peers) K1 first samples 4096 pages: if none of
+ * them is a zero page the image is taken to be dense (weights, optimizer state:
+ * compaction is then the identity) and K1 stores every page to its own slot of
+ * d_packed while analysing it, up to the first zero page it meets; K3 leaves
+ * pages that are already in place where they are.  The result is the same bytes
+ * either way; stats->wrote_through says which way it went. */
 int grit_pack_buffer(grit_ctx *ctx, const void *d_image, uint64_t n_pages,
                      const grit_table *parent, const grit_table *peers,
                      uint32_t n_peers, void *d_packed, uint64_t capacity_pages,

@@ -36,7 +36,7 @@ def test_pack_host_matches_oracle(ctx, oracle, pinned, n_pages):
         t, packed = t.pin_memory(), packed.pin_memory()
     r = ctx.pack_host(t, packed=packed)
     o = oracle.pack(img, threads=8)
-    assert {k: v for k, v in r["stats"].items() if k != "gpu_ms"} == o["stats"]
+    assert {k: v for k, v in r["stats"].items() if k.startswith("n_")} == o["stats"]
     assert np.array_equal(u32(r["ref"]), o["ref"]) and np.array_equal(u32(r["crc"]), o["crc"])
     assert np.array_equal(r["packed"].numpy(), o["packed"])
     out = torch.empty(n_pages * PAGE, dtype=torch.uint8)

@@ -65,7 +65,7 @@ def test_pack_matches_oracle(ctx, oracle, n_pages, kw):
     img = mixed_image(oracle, n_pages, seed=1000 + n_pages, **kw)
     r = ctx.pack(dev(img))
     o = oracle.pack(img)
-    st = {k: v for k, v in r["stats"].items() if k != "gpu_ms"}
+    st = {k: v for k, v in r["stats"].items() if k.startswith("n_")}
     assert st == o["stats"]
     assert np.array_equal(u32(r["ref"]), o["ref"])
     assert np.array_equal(u32(r["crc"]), o["crc"]) and np.array_equal(u64(r["hash"]), o["hash"])
@@ -96,7 +96,7 @@ def test_pack_incremental_against_parent(ctx, oracle):
         child[d * PAGE:(d + 1) * PAGE] = rng.integers(0, 256, PAGE, dtype=np.uint8)
     r = ctx.pack(dev(child), parent=(pb["hash"], pb["crc"]))
     o = oracle.pack(child, parent=(u64(pb["hash"]), u32(pb["crc"])))
-    assert {k: v for k, v in r["stats"].items() if k != "gpu_ms"} == o["stats"] and o["stats"]["n_data"] == 150
+    assert {k: v for k, v in r["stats"].items() if k.startswith("n_")} == o["stats"] and o["stats"]["n_data"] == 150
     assert np.array_equal(u32(r["ref"]), o["ref"]) and np.array_equal(r["packed"].cpu().numpy(), o["packed"])
     out, rs = ctx.restore(r["packed"], r["ref"], r["crc"], parent_image=dev(base))
     assert rs["n_bad"] == 0 and np.array_equal(out.cpu().numpy(), child)
@@ -219,7 +219,7 @@ for n, kw in [(1, {}), (129, {}), (5000, {}), (3000, dict(pct_zero=40, pct_dup=5
     assert np.array_equal(g["ref"].cpu().numpy().view(np.uint32), o["ref"]), n
     assert np.array_equal(g["crc"].cpu().numpy().view(np.uint32), o["crc"]), n
     assert np.array_equal(g["packed"].cpu().numpy(), o["packed"]), n
-    assert {k: v for k, v in g["stats"].items() if k != "gpu_ms"} == o["stats"], n
+    assert {k: v for k, v in g["stats"].items() if k.startswith("n_")} == o["stats"], n
 base = O.synth_image(2000, 9)
 pb = ctx.pack(torch.from_numpy(base).cuda())
 child = base.copy(); child[5 * 4096:6 * 4096] ^= 0xFF
@@ -260,3 +260,32 @@ def test_dedup_rule_on_crafted_tables(ctx):
         4 << 29 | 0 << 26 | 0,   # 6: both peers hold it; the lowest rank owns it
         0,                       # 7: zero page untouched
     ]
+
+
+def test_dense_images_are_written_through_and_mixed_ones_are_not(ctx, oracle):
+    """grit_pack_buffer samples a full image: dense ones (no zero page) are stored to their own slots by K1 and left in
+    place by K3, the others go through plain K1 + K3; a zero page met after the sample said "dense" ends the
+    write-through.  The bytes are the oracle's in every case."""
+    n = 6000
+    dense = oracle.synth_image(n, 31, pct_zero=0, pct_dup=0)
+    late_zero = dense.copy()
+    late_zero[5001 * PAGE:5002 * PAGE] = 0            # not among the 4096 sampled pages? either way the result must hold
+    dups_only = oracle.synth_image(n, 32, pct_zero=0, pct_dup=30, dup_pool=7)
+    mixed = oracle.synth_image(n, 33)
+    for name, img, want_through in (("dense", dense, 1), ("late_zero", late_zero, None), ("dups_only", dups_only, 1),
+                                    ("mixed", mixed, 0)):
+        r = ctx.pack(dev(img))
+        o = oracle.pack(img)
+        assert np.array_equal(u32(r["ref"]), o["ref"]), name
+        assert np.array_equal(r["packed"].cpu().numpy(), o["packed"]), name
+        if want_through is not None:
+            assert r["stats"]["wrote_through"] == want_through, name
+        out, rs = ctx.restore(r["packed"], r["ref"], r["crc"])
+        assert rs["n_bad"] == 0 and np.array_equal(out.cpu().numpy(), img), name
+    # a packed buffer smaller than the image: written-through pages beyond it must not be stored
+    small = torch.empty(100 * PAGE, dtype=torch.uint8, device="cuda")
+    guard = torch.full((PAGE,), 0xAB, dtype=torch.uint8, device="cuda")
+    both = torch.cat([small, guard])                  # guard page right behind the packed buffer
+    with pytest.raises(Exception, match="too small"):
+        ctx.pack(dev(dense), packed=both[: 100 * PAGE])
+    assert bool((both[100 * PAGE:] == 0xAB).all())
