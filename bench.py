@@ -227,7 +227,7 @@ def run_gritpack(args):
         if world == 1:
             return ctx.pack(image, packed=packed, out=meta)
         from grit_b200 import dist as gdist
-        crc, h, ref = ctx.analyze(image)
+        crc, h, ref = ctx.analyze(image, through=packed)
         tables = gdist.all_gather_tables(h, crc, counts=[n_pages] * world)   # NCCL over NVLink: 12 B per 4 KiB page
         ctx.dedup(crc, h, ref, peers=gdist.peers_of(rank, tables))
         n = ctx.compact(image, ref, packed)
@@ -287,9 +287,9 @@ def run_gritpack(args):
         through = bool(r["stats"]["wrote_through"])
     else:
         r = pack_step()
-        k1_ms = timed(lambda: ctx.analyze(image))
+        k1_ms = timed(lambda: ctx.analyze(image, through=packed))
         k2_ms = k3_ms = None
-        through = False
+        through = True   # rank-seeded dense images: K1 writes through, K3 finds the pages in place
     n_data = int(r["stats"]["n_data"])
     U = n_data * PAGE
     t_restore = timed(lambda: ctx.restore(r["packed"], r["ref"], r["crc"], out=restored))

@@ -72,14 +72,21 @@ class Context:
         return img
 
     # -- K1
-    def analyze(self, image):
+    def analyze(self, image, through=None):
+        """K1.  `through`: the packed buffer the following compact() will fill -- dense images are then written
+        through to it while they are analysed (grit_analyze_pages_through)."""
         n = self._pages(image)
         crc = torch.empty(n, dtype=torch.int32, device=image.device)
         h = torch.empty(n, dtype=torch.int64, device=image.device)
         ref = torch.empty(n, dtype=torch.int32, device=image.device)
         err = _lib.errbuf()
-        _lib.check(self.lib.grit_analyze_pages(self.handle, _ptr(image), n, _ptr(crc), _ptr(h), _ptr(ref), _stream(),
-                                               err, len(err)), err)
+        if through is None:
+            rc = self.lib.grit_analyze_pages(self.handle, _ptr(image), n, _ptr(crc), _ptr(h), _ptr(ref), _stream(), err,
+                                             len(err))
+        else:
+            rc = self.lib.grit_analyze_pages_through(self.handle, _ptr(image), n, _ptr(crc), _ptr(h), _ptr(ref),
+                                                     _ptr(through), through.numel() // PAGE, _stream(), err, len(err))
+        _lib.check(rc, err)
         return crc, h, ref
 
     # -- K2

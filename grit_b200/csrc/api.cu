@@ -1,6 +1,7 @@
 // C ABI over the page kernels: context, stage entry points, pack/restore of a
 // device-resident image.  Declarations and reference citations: include/gritpack.h.
 #include <algorithm>
+#include <cstddef>
 #include <cstdlib>
 #include <new>
 
@@ -43,9 +44,8 @@ int ensure_status(grit_ctx* ctx, uint64_t n_pages, char* err, size_t errlen) {
 }
 
 int reset_counters(grit_ctx* ctx, cudaStream_t s, char* err, size_t errlen) {
-  GRIT_CUDA(cudaMemsetAsync(ctx->d_cnt, 0, sizeof(DevCounters), s));
-  GRIT_CUDA(cudaMemsetAsync(&ctx->d_cnt->first_bad, 0xFF, 2 * sizeof(unsigned long long), s));  // first_bad, first_drop
-  GRIT_CUDA(cudaMemsetAsync(&ctx->d_cnt->dense_hint, 1, 1, s));  // little endian: dense_hint = 1
+  GRIT_CUDA(cudaMemsetAsync(ctx->d_cnt, 0, offsetof(DevCounters, first_drop), s));  // not the write-through state
+  GRIT_CUDA(cudaMemsetAsync(&ctx->d_cnt->first_bad, 0xFF, sizeof(unsigned long long), s));
   return GRIT_OK;
 }
 
@@ -178,9 +178,29 @@ int dedup_async(grit_ctx* ctx, uint64_t n_pages, const uint32_t* d_crc, const ui
   return GRIT_OK;
 }
 
+// K1 with the dense sample and write-through into d_packed; remembers the buffers for the K3 that follows
+int analyze_through_async(grit_ctx* ctx, const void* d_image, uint64_t n_pages, uint32_t* d_crc, uint64_t* d_hash,
+                          uint32_t* d_ref, void* d_packed, uint64_t capacity_pages, cudaStream_t s, char* err,
+                          size_t errlen) {
+  GRIT_CUDA(cudaMemsetAsync(&ctx->d_cnt->first_drop, 0xFF, sizeof(unsigned long long), s));
+  GRIT_CUDA(cudaMemsetAsync(&ctx->d_cnt->dense_hint, 0, sizeof(unsigned int), s));
+  GRIT_CUDA(cudaMemsetAsync(&ctx->d_cnt->dense_hint, 1, 1, s));  // little endian: dense_hint = 1
+  GRIT_CUDA(launch_analyze_auto(ctx->geom, ctx->d_tables, d_image, n_pages, d_crc, d_hash, d_ref, d_packed, capacity_pages,
+                                ctx->d_cnt, s));
+  ctx->launches += 3;
+  ctx->through_image = d_image;
+  ctx->through_packed = d_packed;
+  ctx->through_pages = n_pages;
+  return GRIT_OK;
+}
+
 int compact_async(grit_ctx* ctx, const void* d_image, uint64_t n_pages, uint32_t* d_ref, void* d_packed,
-                  uint64_t capacity_pages, uint64_t slot_base, cudaStream_t s, char* err, size_t errlen,
-                  bool in_place = false) {
+                  uint64_t capacity_pages, uint64_t slot_base, cudaStream_t s, char* err, size_t errlen) {
+  // pages that the write-through K1 of these very buffers put at their own index stay where they are
+  const bool in_place = n_pages && slot_base == 0 && ctx->through_image == d_image && ctx->through_packed == d_packed &&
+                        ctx->through_pages == n_pages;
+  ctx->through_image = ctx->through_packed = nullptr;
+  ctx->through_pages = 0;
   if (int rc = ensure_status(ctx, n_pages, err, errlen)) return rc;
   const uint64_t tiles = (n_pages + kCompactTile - 1) / kCompactTile;
   GRIT_CUDA(cudaMemsetAsync(ctx->d_status, 0, tiles * sizeof(unsigned long long), s));
@@ -280,9 +300,23 @@ int grit_analyze_pages(grit_ctx* ctx, const void* d_image, uint64_t n_pages, uin
   if (int rc = check_pages(n_pages, d_image, err, errlen)) return rc;
   if (n_pages && (!d_image || !d_crc || !d_hash || !d_ref)) return fail(err, errlen, GRIT_EINVAL, "null buffer");
   std::lock_guard<std::mutex> g(ctx->mu);
+  ctx->through_image = nullptr;
   GRIT_CUDA(launch_analyze(ctx->geom, ctx->d_tables, d_image, n_pages, d_crc, d_hash, d_ref, pick(ctx, stream)));
   ctx->launches++;
   return GRIT_OK;
+}
+
+int grit_analyze_pages_through(grit_ctx* ctx, const void* d_image, uint64_t n_pages, uint32_t* d_crc, uint64_t* d_hash,
+                               uint32_t* d_ref, void* d_packed, uint64_t capacity_pages, void* stream, char* err,
+                               size_t errlen) {
+  if (int rc = enter(ctx, err, errlen)) return rc;
+  if (int rc = check_pages(n_pages, d_image, err, errlen)) return rc;
+  if (int rc = check_pages(0, d_packed, err, errlen)) return rc;
+  if (n_pages && (!d_image || !d_crc || !d_hash || !d_ref || !d_packed)) return fail(err, errlen, GRIT_EINVAL, "null buffer");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  if (!n_pages) return GRIT_OK;
+  return analyze_through_async(ctx, d_image, n_pages, d_crc, d_hash, d_ref, d_packed, capacity_pages, pick(ctx, stream), err,
+                               errlen);
 }
 
 int grit_dedup_pages(grit_ctx* ctx, uint64_t n_pages, const uint32_t* d_crc, const uint64_t* d_hash, uint32_t* d_ref,
@@ -331,12 +365,12 @@ int grit_pack_buffer(grit_ctx* ctx, const void* d_image, uint64_t n_pages, const
     // A full (not incremental, single-rank) image may be dense -- weights, optimizer state: no zero pages,
     // no duplicates -- and then compaction is the identity: K1 writes such pages through to their own
     // slot and K3 finds them in place.  A sample of the image decides, on the device.
-    const bool try_through = !(parent && parent->n_pages) && n_peers == 0 && d_packed && write_through_pack();
+    const bool try_through = n_pages && !(parent && parent->n_pages) && n_peers == 0 && d_packed && write_through_pack();
     if (try_through) {
-      GRIT_CUDA(launch_analyze_auto(ctx->geom, ctx->d_tables, d_image, n_pages, d_crc, d_hash, d_ref, d_packed,
-                                    capacity_pages, ctx->d_cnt, s));
-      ctx->launches += 3;
+      if (int rc = analyze_through_async(ctx, d_image, n_pages, d_crc, d_hash, d_ref, d_packed, capacity_pages, s, err, errlen))
+        return rc;
     } else {
+      ctx->through_image = nullptr;
       GRIT_CUDA(launch_analyze(ctx->geom, ctx->d_tables, d_image, n_pages, d_crc, d_hash, d_ref, s));
       ctx->launches++;
     }
@@ -344,7 +378,7 @@ int grit_pack_buffer(grit_ctx* ctx, const void* d_image, uint64_t n_pages, const
     if (int rc = dedup_async(ctx, n_pages, d_crc, d_hash, d_ref, parent, peers, n_peers, s, err, errlen)) return rc;
     GRIT_CUDA(cudaEventRecord(ctx->evB, s));
     staged = true;
-    if (int rc = compact_async(ctx, d_image, n_pages, d_ref, d_packed, capacity_pages, 0, s, err, errlen, try_through)) return rc;
+    if (int rc = compact_async(ctx, d_image, n_pages, d_ref, d_packed, capacity_pages, 0, s, err, errlen)) return rc;
   } else if (n_pages) {
     DedupTable t{};
     PeerCrcs crcs{};

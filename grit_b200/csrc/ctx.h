@@ -28,6 +28,10 @@ struct grit_ctx {
   uint64_t status_cap = 0;
   uint64_t launches = 0;
   std::mutex mu;
+  // the last write-through K1 on this context: K3 on the same image and packed buffer leaves pages in place
+  const void* through_image = nullptr;
+  const void* through_packed = nullptr;
+  uint64_t through_pages = 0;
   // Working buffers of the host pipelines, kept between calls (grown on demand, freed with the
   // context) so that a steady stream of packs/restores does no cudaMalloc/cudaFree at all.
   struct Buf {

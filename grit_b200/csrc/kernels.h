@@ -42,13 +42,17 @@ struct DevCounters {
   unsigned long long overflow;   // pages that did not fit capacity_pages
   unsigned long long n_bad;      // restore: pages that failed
   unsigned long long first_bad;  // restore: lowest such page
-  unsigned long long first_drop;      // write-through K1: lowest zero page seen so far (UINT64_MAX: none)
   unsigned long long slot_base;       // compact, chained mode: first slot of this launch
   unsigned long long slot_base_next;  // compact: slot_base + pages stored by this launch
   unsigned int ticket;                // compact / fused pack: next tile to analyse
   unsigned int copy_ticket;           // fused pack: next tile whose pages are decided and copied
   unsigned int watermark;             // fused pack: tiles [0, watermark) have entered their hashes in the table
-  unsigned int dense_hint;            // 1: the sampled pages held no zero page, K1 writes through
+  unsigned int pad;
+  // --- owned by the write-through K1 (grit_analyze_pages_through); not touched by the per-call reset,
+  // so that a later K3 on the same buffers can see how K1 went
+  unsigned long long first_drop;      // lowest zero page K1 has seen (UINT64_MAX: none); storing stops above it
+  unsigned int dense_hint;            // 1: the sampled pages held no zero page and K1 wrote the pages through
+  unsigned int pad2;
 };
 
 struct LaunchGeom {

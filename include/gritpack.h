@@ -122,6 +122,21 @@ int grit_analyze_pages(grit_ctx *ctx, const void *d_image, uint64_t n_pages,
                        uint32_t *d_crc, uint64_t *d_hash, uint32_t *d_ref,
                        void *stream, char *err, size_t errlen);
 
+/* K1 for a caller that will run K3 next on the same image with d_packed as the
+ * target (grit_compact_pages, slot_base 0): same results as grit_analyze_pages,
+ * and if a 4096-page sample of the image holds no zero page, every page is also
+ * stored to d_packed at its own index, up to the first zero page met
+ * (capacity_pages bounds the stores).  The context remembers the two buffers;
+ * the next grit_compact_pages on them leaves in place every page whose slot is
+ * its own index, which for a dense image (weights, optimizer state) is all of
+ * them: the image is then read once and written once.  Any other analyze, pack
+ * or compact call on the context forgets the buffers.  No reference counterpart. */
+int grit_analyze_pages_through(grit_ctx *ctx, const void *d_image,
+                               uint64_t n_pages, uint32_t *d_crc,
+                               uint64_t *d_hash, uint32_t *d_ref,
+                               void *d_packed, uint64_t capacity_pages,
+                               void *stream, char *err, size_t errlen);
+
 /* K2: dedup.  Input: the arrays K1 wrote.  Output: d_ref[p] becomes ZERO, DUP,
  * PARENT, PEER, or 0xFFFFFFFE for a page that must be stored.  The owner of a
  * hash64 is the lowest (parent, peer rank 0.., this image) x page index; a

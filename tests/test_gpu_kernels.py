@@ -289,3 +289,36 @@ def test_dense_images_are_written_through_and_mixed_ones_are_not(ctx, oracle):
     with pytest.raises(Exception, match="too small"):
         ctx.pack(dev(dense), packed=both[: 100 * PAGE])
     assert bool((both[100 * PAGE:] == 0xAB).all())
+
+
+def test_stage_level_write_through(ctx, oracle):
+    """K1 with a packed target, K2, K3 called one by one: same bytes as the oracle whether the image is dense (pages in
+    place after K1) or not, with peers in between, and when the remembered buffers are not the ones K3 gets."""
+    dense = oracle.synth_image(5000, 51, pct_zero=0, pct_dup=0)
+    mixed = oracle.synth_image(5000, 52)
+    for img in (dense, mixed):
+        d = dev(img)
+        packed = torch.zeros_like(d)
+        crc, h, ref = ctx.analyze(d, through=packed)
+        if img is dense:
+            assert torch.equal(packed, d)                       # already there after K1
+        ctx.dedup(crc, h, ref)
+        n = ctx.compact(d, ref, packed)
+        o = oracle.pack(img)
+        assert n == o["stats"]["n_data"] and np.array_equal(u32(ref), o["ref"])
+        assert np.array_equal(packed[: n * PAGE].cpu().numpy(), o["packed"])
+    # a lower rank holds the first 1000 pages: they become PEER references, everything behind them moves up
+    d = dev(dense)
+    packed = torch.zeros_like(d)
+    crc, h, ref = ctx.analyze(d, through=packed)
+    peer = (h[:1000].clone(), crc[:1000].clone())
+    ctx.dedup(crc, h, ref, peers=[peer])
+    n = ctx.compact(d, ref, packed)
+    o = oracle.pack(dense, peers=[(u64(peer[0]), u32(peer[1]))])
+    assert n == 4000 and np.array_equal(u32(ref), o["ref"]) and np.array_equal(packed[: n * PAGE].cpu().numpy(), o["packed"])
+    # K3 on other buffers than the ones K1 wrote through to must copy everything itself
+    crc, h, ref = ctx.analyze(d, through=packed)
+    ctx.dedup(crc, h, ref)
+    other = torch.zeros_like(d)
+    n = ctx.compact(d, ref, other)
+    assert n == 5000 and torch.equal(other, d)
