@@ -322,3 +322,31 @@ def test_stage_level_write_through(ctx, oracle):
     other = torch.zeros_like(d)
     n = ctx.compact(d, ref, other)
     assert n == 5000 and torch.equal(other, d)
+
+
+def test_bad_arguments_are_refused_with_a_message(ctx):
+    import ctypes as C
+    from grit_b200 import _lib
+    lib = _lib.load()
+    img = torch.zeros(4 * PAGE + 16, dtype=torch.uint8, device="cuda")
+    crc = torch.zeros(4, dtype=torch.int32, device="cuda")
+    h = torch.zeros(4, dtype=torch.int64, device="cuda")
+    ref = torch.zeros(4, dtype=torch.int32, device="cuda")
+    err = _lib.errbuf()
+    p = lambda t, off=0: C.c_void_p(t.data_ptr() + off)
+    # misaligned image
+    assert lib.grit_analyze_pages(ctx.handle, p(img, 8), 4, p(crc), p(h), p(ref), None, err, len(err)) == _lib.EINVAL
+    assert b"aligned" in err.value
+    # null output
+    assert lib.grit_analyze_pages(ctx.handle, p(img), 4, None, p(h), p(ref), None, err, len(err)) == _lib.EINVAL
+    # more pages than the format can number
+    assert lib.grit_analyze_pages(ctx.handle, p(img), (1 << 26) + 1, p(crc), p(h), p(ref), None, err, len(err)) == _lib.EINVAL
+    assert b"GRIT_MAX_PAGES" in err.value
+    # too many peers
+    tabs = (_lib.Table * 9)()
+    assert lib.grit_dedup_pages(ctx.handle, 4, p(crc), p(h), p(ref), None, tabs, 9, None, err, len(err)) == _lib.EINVAL
+    # null context
+    assert lib.grit_analyze_pages(None, p(img), 4, p(crc), p(h), p(ref), None, err, len(err)) == _lib.EINVAL
+    # a device that does not exist
+    hnd = C.c_void_p()
+    assert lib.grit_ctx_create(99, C.byref(hnd), err, len(err)) == _lib.EINVAL and b"out of range" in err.value
