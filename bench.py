@@ -44,35 +44,54 @@ def measured_peak():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md clocks line)."""
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md clocks line).
+
+    nvidia-smi takes a while to start, so it is started early (before the warm-up) and keeps running; every line is
+    stamped on arrival and mark_begin() / mark_end() bracket the timed region: only samples taken inside it count."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.index, self.proc, self.lines = index, None, []
+        self.index, self.proc, self.lines, self.t0, self.t1 = index, None, [], None, None
 
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "40"],
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            threading.Thread(target=lambda: self.lines.extend(self.proc.stdout), daemon=True).start()
+
+            def pump():
+                for ln in self.proc.stdout:
+                    self.lines.append((time.time(), ln))
+            threading.Thread(target=pump, daemon=True).start()
         except Exception:
             self.proc = None
+
+    def wait_first_sample(self, timeout=10.0):
+        t = time.time()
+        while self.proc and not self.lines and time.time() - t < timeout:
+            time.sleep(0.01)
+
+    def mark_begin(self):
+        self.t0 = time.time()
+
+    def mark_end(self):
+        self.t1 = time.time()
 
     def stop(self):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
+        time.sleep(0.05)
         self.proc.terminate()
         try:
             self.proc.wait(timeout=5)
         except Exception:
             self.proc.kill()
+        inside = [ln for (t, ln) in self.lines if self.t0 is not None and self.t0 <= t <= (self.t1 or t) + 0.03]
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        for ln in inside:
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 7:
                 continue
@@ -86,7 +105,8 @@ class ClockSampler:
                     reasons.add(n)
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+                "samples": len(sm), "reasons": sorted(reasons),
+                "how": "nvidia-smi -lms 20 started before the warm-up; samples stamped inside the timed region only"}
 
 
 # ----------------------------------------------------------------------------- reference arm
@@ -239,20 +259,25 @@ def run_gritpack(args):
         return r
 
     # ---- value: device-resident, K timed steps, CUDA events, max over ranks
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
     for _ in range(max(args.warmup, 3)):
         r = step()
     assert torch.equal(restored, image), "restored image differs from the source image"
-    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.wait_first_sample()
     launches0 = ctx.launches
     barrier()
-    sampler.start()
+    sampler.mark_begin()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(args.steps):
         step()
     e1.record()
     barrier()
-    clocks = sampler.stop()
+    sampler.mark_end()
+    clocks = sampler.stop() if rank == 0 else None
     launches = ctx.launches - launches0
     ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
     if world > 1:
@@ -490,7 +515,7 @@ def run_gritpack(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=40)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="gritpack", choices=["gritpack", "reference"])
     ap.add_argument("--pages", type=int, default=0, help="override pages per GPU (debug only; invalid as a bench number)")
