@@ -16,7 +16,10 @@ from ._lib import GritError, Opts, Stats
 UPLOAD, DOWNLOAD = "upload", "download"
 
 
-def _opts(device=0, verify=True, io_threads=0, chunk_bytes=0, parent_dir=None):
+def _opts(device=0, verify=True, io_threads=0, chunk_bytes=0, parent_dir=None, peers=()):
+    """peers: [(hash64 array, crc32c array, packed_dir)] of the ranks below this one, in rank order -- numpy arrays
+    (uint64 / uint32), e.g. from grit_b200.dist.all_gather_tables or read_tables() of the lower ranks' directories."""
+    import numpy as np
     o = Opts()
     o.struct_size = C.sizeof(Opts)
     o.device = device
@@ -24,7 +27,27 @@ def _opts(device=0, verify=True, io_threads=0, chunk_bytes=0, parent_dir=None):
     o.io_threads = io_threads
     o.chunk_bytes = chunk_bytes
     o.parent_dir = os.fsencode(parent_dir) if parent_dir else None
+    if peers:
+        keep = []
+        tabs = (_lib.Table * len(peers))()
+        dirs = (C.c_char_p * len(peers))()
+        for i, (h, crc, d) in enumerate(peers):
+            h = np.ascontiguousarray(h, dtype=np.uint64)
+            crc = np.ascontiguousarray(crc, dtype=np.uint32)
+            keep += [h, crc]
+            tabs[i] = _lib.Table(h.ctypes.data, crc.ctypes.data, h.size)
+            dirs[i] = os.fsencode(d)
+        o.n_peers, o.peer_tables, o.peer_dirs = len(peers), tabs, dirs
+        o._keep = (keep, tabs, dirs)
     return o
+
+
+def read_tables(packed_dir):
+    """(hash64, crc32c) per page of a packed directory, from its hashes.bin / pagemap.bin."""
+    import numpy as np
+    h = np.fromfile(os.path.join(packed_dir, "hashes.bin"), np.uint64)
+    pm = np.fromfile(os.path.join(packed_dir, "pagemap.bin"), np.uint32)
+    return h, pm[h.size:]
 
 
 def TransferData(src_dir, dst_dir, direction, **kw):

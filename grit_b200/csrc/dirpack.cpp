@@ -37,7 +37,7 @@ using namespace grit;
 namespace {
 
 constexpr char kMagic[8] = {'G', 'R', 'I', 'T', 'P', 'A', 'K', '1'};
-constexpr uint32_t kFormatVersion = 2;
+constexpr uint32_t kFormatVersion = 3;
 const char* const kManifest = "gritpack.manifest";
 
 struct Entry {
@@ -54,6 +54,7 @@ struct Manifest {
   uint32_t pagemap_crc = 0, hashes_crc = 0;
   uint32_t n_shards = 8, stripe_slots = 2048;  // layout of the stored pages over pages-NNN.bin
   std::string parent;
+  std::vector<std::string> peers;  // packed directories of ranks 0..n-1 that PEER references point into
 };
 
 std::string errno_msg(const char* op, const std::string& path) {
@@ -160,6 +161,11 @@ std::string encode_manifest(const Manifest& m) {
   put<uint32_t>(&b, m.stripe_slots);
   put<uint32_t>(&b, (uint32_t)m.parent.size());
   put(&b, m.parent.data(), m.parent.size());
+  put<uint32_t>(&b, (uint32_t)m.peers.size());
+  for (const auto& p : m.peers) {
+    put<uint32_t>(&b, (uint32_t)p.size());
+    put(&b, p.data(), p.size());
+  }
   for (const auto& e : m.entries) {
     put<uint8_t>(&b, e.type);
     put<uint32_t>(&b, e.mode);
@@ -236,7 +242,7 @@ bool has_manifest(const std::string& dir) {
 int load_manifest(const std::string& dir, Manifest* m, std::string* msg) {
   std::string b;
   if (int rc = read_file(dir + "/" + kManifest, &b, msg)) return rc;
-  if (b.size() < 8 + 4 * 2 + 8 * 3 + 4 * 5 + 4 || memcmp(b.data(), kMagic, 8))
+  if (b.size() < 8 + 4 * 2 + 8 * 3 + 4 * 6 + 4 || memcmp(b.data(), kMagic, 8))
     return *msg = dir + ": not a gritpack manifest", GRIT_EFORMAT;
   uint32_t want;
   memcpy(&want, b.data() + b.size() - 4, 4);
@@ -253,6 +259,9 @@ int load_manifest(const std::string& dir, Manifest* m, std::string* msg) {
   m->stripe_slots = r.get<uint32_t>();
   if (m->n_shards == 0 || m->n_shards > 256 || m->stripe_slots == 0) return *msg = dir + ": bad page store layout", GRIT_EFORMAT;
   m->parent = r.str(r.get<uint32_t>());
+  const uint32_t n_peer_dirs = r.get<uint32_t>();
+  if (n_peer_dirs > GRIT_MAX_PEERS) return *msg = dir + ": bad peer list", GRIT_EFORMAT;
+  for (uint32_t i = 0; i < n_peer_dirs && r.ok; i++) m->peers.push_back(r.str(r.get<uint32_t>()));
   for (uint32_t i = 0; i < n_entries && r.ok; i++) {
     Entry e;
     e.type = r.get<uint8_t>();
@@ -470,6 +479,9 @@ struct Opts {
   unsigned io_threads = 8;
   uint64_t chunk_pages = 0;  // 0: chosen from the image size
   std::string parent;
+  uint32_t n_peers = 0;
+  const grit_table* peer_tables = nullptr;
+  std::vector<std::string> peer_dirs;
   // 64 MiB chunks for big images; small images get smaller chunks so that the pinned staging
   // (six chunks) does not cost more to allocate than the image costs to move
   uint64_t chunk_for(uint64_t n_pages) const {
@@ -487,6 +499,11 @@ Opts read_opts(const grit_opts* o) {
   if (o->io_threads) r.io_threads = o->io_threads;
   if (o->chunk_bytes >= (1u << 20)) r.chunk_pages = o->chunk_bytes / kPage;
   if (o->parent_dir) r.parent = o->parent_dir;
+  if (o->struct_size >= sizeof(grit_opts) && o->n_peers && o->peer_tables && o->peer_dirs) {
+    r.n_peers = o->n_peers;
+    r.peer_tables = o->peer_tables;
+    for (uint32_t i = 0; i < o->n_peers; i++) r.peer_dirs.emplace_back(o->peer_dirs[i] ? o->peer_dirs[i] : "");
+  }
   return r;
 }
 
@@ -495,10 +512,24 @@ struct CtxGuard {
   ~CtxGuard() { grit_ctx_destroy(ctx); }
 };
 
-// Restores the whole image of a packed directory into device memory (used for
-// parents of incremental checkpoints).  Follows the parent chain recursively.
-int image_to_device(grit_ctx* ctx, const std::string& dir, int verify, void** d_image, uint64_t* n_pages, int depth,
-                    grit_stats* stats, std::string* msg);
+// Fully restored images of other packed directories (parents of incremental checkpoints, lower ranks of a
+// multi-GPU job), kept on the device while a restore refers to them.  An image may itself refer to a parent
+// and to lower ranks; each directory is loaded once.
+struct ImageCache {
+  struct Img {
+    void* d = nullptr;
+    uint64_t pages = 0;
+  };
+  std::vector<std::pair<std::string, Img>> items;
+  ~ImageCache() {
+    for (auto& it : items) cudaFree(it.second.d);
+  }
+  const Img* find(const std::string& dir) const {
+    for (auto& it : items)
+      if (it.first == dir) return &it.second;
+    return nullptr;
+  }
+};
 
 std::string resolve_parent(const std::string& child_dir, const std::string& parent) {
   if (has_manifest(parent)) return parent;
@@ -511,18 +542,54 @@ std::string resolve_parent(const std::string& child_dir, const std::string& pare
   return has_manifest(sib) ? sib : parent;
 }
 
-int image_to_device(grit_ctx* ctx, const std::string& dir, int verify, void** d_image, uint64_t* n_pages, int depth,
-                    grit_stats* stats, std::string* msg) {
-  if (depth > 64) return *msg = "parent chain too deep", GRIT_EFORMAT;
+// which lower ranks the page map refers to; an error if it names a rank the manifest does not list
+int peers_used(const Manifest& m, const std::vector<uint32_t>& ref, bool (&used)[GRIT_MAX_PEERS], std::string* msg) {
+  for (uint64_t p = 0; p < m.n_pages; p++)
+    if (GRIT_REF_KIND(ref[p]) == GRIT_KIND_PEER) {
+      const uint32_t rk = GRIT_REF_VALUE(ref[p]) >> 26;
+      if (rk >= m.peers.size())
+        return *msg = "page " + std::to_string(p) + " refers to rank " + std::to_string(rk) + ", which the manifest does not name",
+               GRIT_EFORMAT;
+      used[rk] = true;
+    }
+  return GRIT_OK;
+}
+
+int image_to_device(grit_ctx* ctx, const std::string& dir, int verify, ImageCache* cache, const ImageCache::Img** out,
+                    int depth, grit_stats* stats, std::string* msg);
+
+// parent and peer images a page map needs, from the cache
+int load_dependencies(grit_ctx* ctx, const std::string& dir, const Manifest& m, const std::vector<uint32_t>& ref, int verify,
+                      ImageCache* cache, int depth, grit_stats* stats, const ImageCache::Img** parent, PeerImages* peers,
+                      std::string* msg) {
+  *parent = nullptr;
+  if (!m.parent.empty())
+    if (int rc = image_to_device(ctx, resolve_parent(dir, m.parent), verify, cache, parent, depth + 1, stats, msg)) return rc;
+  bool used[GRIT_MAX_PEERS] = {};
+  if (int rc = peers_used(m, ref, used, msg)) return *msg = dir + ": " + *msg, rc;
+  *peers = PeerImages{};
+  peers->n_peers = (uint32_t)m.peers.size();
+  for (uint32_t r = 0; r < m.peers.size(); r++) {
+    if (!used[r]) continue;
+    const ImageCache::Img* img = nullptr;
+    if (int rc = image_to_device(ctx, resolve_parent(dir, m.peers[r]), verify, cache, &img, depth + 1, stats, msg)) return rc;
+    peers->peer[r] = static_cast<const unsigned char*>(img->d);
+    peers->peer_pages[r] = img->pages;
+  }
+  return GRIT_OK;
+}
+
+int image_to_device(grit_ctx* ctx, const std::string& dir, int verify, ImageCache* cache, const ImageCache::Img** out,
+                    int depth, grit_stats* stats, std::string* msg) {
+  if (const ImageCache::Img* hit = cache->find(dir)) return *out = hit, GRIT_OK;
+  if (depth > 64) return *msg = "parent / peer chain too deep", GRIT_EFORMAT;
   Manifest m;
   if (int rc = load_manifest(dir, &m, msg)) return rc;
   std::vector<uint32_t> ref, crc;
   if (int rc = load_pagemap(dir, m, &ref, &crc, msg)) return rc;
-  void* d_parent = nullptr;
-  uint64_t parent_pages = 0;
-  if (!m.parent.empty())
-    if (int rc = image_to_device(ctx, resolve_parent(dir, m.parent), verify, &d_parent, &parent_pages, depth + 1, stats, msg))
-      return rc;
+  const ImageCache::Img* parent = nullptr;
+  PeerImages peers{};
+  if (int rc = load_dependencies(ctx, dir, m, ref, verify, cache, depth, stats, &parent, &peers, msg)) return rc;
   char err[512] = "";
   const size_t errlen = sizeof err;
   void *d_packed = nullptr, *d_out = nullptr;
@@ -531,7 +598,6 @@ int image_to_device(grit_ctx* ctx, const std::string& dir, int verify, void** d_
     cudaFree(d_packed);
     cudaFree(d_ref);
     cudaFree(d_crc);
-    cudaFree(d_parent);
   };
   auto body = [&]() -> int {
     GRIT_CUDA(cudaMalloc(&d_packed, std::max<uint64_t>(m.n_slots, 1) * kPage));
@@ -561,9 +627,12 @@ int image_to_device(grit_ctx* ctx, const std::string& dir, int verify, void** d_
     if (rc) return rc;
     GRIT_CUDA(cudaMemcpy(d_ref, ref.data(), m.n_pages * 4, cudaMemcpyHostToDevice));
     GRIT_CUDA(cudaMemcpy(d_crc, crc.data(), m.n_pages * 4, cudaMemcpyHostToDevice));
+    const void* peer_ptrs[GRIT_MAX_PEERS];
+    for (uint32_t r = 0; r < GRIT_MAX_PEERS; r++) peer_ptrs[r] = peers.peer[r];
     grit_restore_stats rs{};
-    rc = grit_restore_buffer(ctx, d_packed, m.n_slots, d_ref, d_crc, m.n_pages, d_parent, parent_pages, nullptr, nullptr,
-                             0, d_out, verify, &rs, nullptr, err, errlen);
+    rc = grit_restore_buffer(ctx, d_packed, m.n_slots, d_ref, d_crc, m.n_pages, parent ? parent->d : nullptr,
+                             parent ? parent->pages : 0, peer_ptrs, peers.peer_pages, peers.n_peers, d_out, verify, &rs,
+                             nullptr, err, errlen);
     if (stats) {
       stats->gpu_ms += rs.gpu_ms;
       stats->n_bad += rs.n_bad;
@@ -577,8 +646,8 @@ int image_to_device(grit_ctx* ctx, const std::string& dir, int verify, void** d_
     *msg = dir + ": " + err;
     return rc;
   }
-  *d_image = d_out;
-  *n_pages = m.n_pages;
+  cache->items.push_back({dir, ImageCache::Img{d_out, m.n_pages}});
+  *out = &cache->items.back().second;
   return GRIT_OK;
 }
 
@@ -650,7 +719,8 @@ int grit_pack_dir(const char* src_dir, const char* dst_dir, const grit_opts* opt
   {
     PackStream pk(ctx, m.n_pages, o.chunk_for(m.n_pages));
     pk.set_outputs(ref.data(), crc.data(), hash.data());
-    if (int rc = pk.begin(parent.n_pages ? &parent : nullptr, err, errlen)) return rc;
+    if (o.n_peers > GRIT_MAX_PEERS) return fail(err, errlen, GRIT_EINVAL, "n_peers %u > %u", o.n_peers, GRIT_MAX_PEERS);
+    if (int rc = pk.begin(parent.n_pages ? &parent : nullptr, err, errlen, o.peer_tables, o.n_peers)) return rc;
     if (m.n_pages)
       if (int rc = pk.alloc_staging(true, true, err, errlen)) return rc;
     const uint64_t cp = pk.chunk_pages(), n_chunks = (m.n_pages + cp - 1) / cp;
@@ -741,7 +811,8 @@ int grit_pack_dir(const char* src_dir, const char* dst_dir, const grit_opts* opt
     st.h2d_bytes = pk.h2d_bytes;
     st.d2h_bytes = pk.d2h_bytes;
   }
-  if (ps.n_peer) return fail(err, errlen, GRIT_EINVAL, "internal: peer references in a single-rank pack");
+  if (ps.n_peer && !o.n_peers) return fail(err, errlen, GRIT_EINVAL, "internal: peer references in a single-rank pack");
+  m.peers = o.peer_dirs;
   ph.mark("finish+free");
   m.n_slots = ps.n_data;
   if (store.sync_all()) return fail(err, errlen, GRIT_EIO, "%s", errno_msg("fsync", store.dir + "/pages-*.bin").c_str());
@@ -804,26 +875,19 @@ int restore_or_verify(const char* src_dir, const char* dst_dir, const grit_opts*
   if (int rc = load_manifest(src, &m, &msg)) return fail(err, errlen, rc, "%s", msg.c_str());
   std::vector<uint32_t> ref, crc;
   if (int rc = load_pagemap(src, m, &ref, &crc, &msg)) return fail(err, errlen, rc, "%s", msg.c_str());
-  for (uint64_t p = 0; p < m.n_pages; p++)
-    if (GRIT_REF_KIND(ref[p]) == GRIT_KIND_PEER)
-      return fail(err, errlen, GRIT_EFORMAT, "%s: page %llu refers to a peer rank's image", src_dir, (unsigned long long)p);
-
-  ph.mark("manifest");
   CtxGuard cg;
   if (int rc = grit_ctx_create(o.device, &cg.ctx, err, errlen)) return rc;
   grit_ctx* ctx = cg.ctx;
   ph.mark("ctx");
 
-  void* d_parent = nullptr;
-  uint64_t parent_pages = 0;
-  struct DevGuard {
-    void** p;
-    ~DevGuard() { cudaFree(*p); }
-  } parent_guard{&d_parent};
-  if (!m.parent.empty()) {
-    if (int rc = image_to_device(ctx, resolve_parent(src, m.parent), o.verify, &d_parent, &parent_pages, 0, &st, &msg))
-      return fail(err, errlen, rc, "parent: %s", msg.c_str());
-  }
+  // what this image refers to: the previous checkpoint, lower ranks' images on the shared PV
+  ImageCache cache;
+  const ImageCache::Img* parent_img = nullptr;
+  PeerImages peer_imgs{};
+  if (int rc = load_dependencies(ctx, src, m, ref, o.verify, &cache, 0, &st, &parent_img, &peer_imgs, &msg))
+    return fail(err, errlen, rc, "%s", msg.c_str());
+  void* d_parent = parent_img ? parent_img->d : nullptr;
+  const uint64_t parent_pages = parent_img ? parent_img->pages : 0;
 
   // tree skeleton: directories 0777 & ~umask (copy.go:36), files created and sized
   if (writing && mkdir_all(dst) != 0) return fail(err, errlen, GRIT_EIO, "%s", errno_msg("mkdir", dst).c_str());
@@ -869,7 +933,7 @@ int restore_or_verify(const char* src_dir, const char* dst_dir, const grit_opts*
   {
     std::lock_guard<std::mutex> g(ctx->mu);
     const int rc = restore_stream(ctx, io, m.n_slots, ref.data(), crc.data(), m.n_pages, d_parent, parent_pages, true,
-                                  o.verify, o.chunk_for(m.n_pages), &rs, &st.h2d_bytes, &st.d2h_bytes, err, errlen);
+                                  o.verify, o.chunk_for(m.n_pages), &rs, &st.h2d_bytes, &st.d2h_bytes, err, errlen, &peer_imgs);
     st.n_bad += rs.n_bad;
     if (rc) {
       if (!msg.empty() && err && errlen) snprintf(err, errlen, "%s", msg.c_str());
@@ -900,6 +964,7 @@ int restore_or_verify(const char* src_dir, const char* dst_dir, const grit_opts*
       case GRIT_KIND_DATA: st.n_data++; break;
       case GRIT_KIND_DUP: st.n_dup++; break;
       case GRIT_KIND_PARENT: st.n_parent++; break;
+      case GRIT_KIND_PEER: st.n_peer++; break;
       default: break;
     }
   }

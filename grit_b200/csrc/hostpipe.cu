@@ -54,10 +54,11 @@ PackStream::~PackStream() {
     if (ev_kern_[b]) cudaEventDestroy(ev_kern_[b]);
     if (ev_d2h_[b]) cudaEventDestroy(ev_d2h_[b]);
   }
-  // the buffers belong to the context's cache and stay for the next call
+  for (void* p : d_peer_bufs_) cudaFree(p);
+  // the other buffers belong to the context's cache and stay for the next call
 }
 
-int PackStream::begin(const grit_table* parent, char* err, size_t errlen) {
+int PackStream::begin(const grit_table* parent, char* err, size_t errlen, const grit_table* peers, uint32_t n_peers) {
   GRIT_CUDA(cudaSetDevice(ctx_->device));
   if (total_pages_ > GRIT_MAX_PAGES) return fail(err, errlen, GRIT_EINVAL, "image exceeds GRIT_MAX_PAGES");
   const size_t chunk_bytes = chunk_pages_ * kPage;
@@ -86,6 +87,11 @@ int PackStream::begin(const grit_table* parent, char* err, size_t errlen) {
     crcs_.parent = d_parent_crc_;
     h2d_bytes += parent->n_pages * 12.0;
   }
+  if (n_peers > GRIT_MAX_PEERS) return fail(err, errlen, GRIT_EINVAL, "n_peers %u > %u", n_peers, GRIT_MAX_PEERS);
+  for (uint32_t r = 0; r < n_peers; r++) {
+    if (peers[r].n_pages > GRIT_MAX_PAGES) return fail(err, errlen, GRIT_EINVAL, "peer exceeds GRIT_MAX_PAGES");
+    items += peers[r].n_pages;
+  }
   if (int rc = ensure_table(ctx_, items, &table_, err, errlen)) return rc;
   if (int rc = ensure_status(ctx_, chunk_pages_, err, errlen)) return rc;
   cudaStream_t s = ctx_->stream;
@@ -94,6 +100,20 @@ int PackStream::begin(const grit_table* parent, char* err, size_t errlen) {
   GRIT_CUDA(cudaMemsetAsync(table_.vals, 0xFF, (table_.mask + 1) * sizeof(uint32_t), s));
   if (parent && parent->n_pages) {
     GRIT_CUDA(launch_table_insert(ctx_->geom, table_, d_parent_hash_, nullptr, parent->n_pages, 0, 0, s));
+    ctx_->launches++;
+  }
+  for (uint32_t r = 0; r < n_peers; r++) {
+    if (!peers[r].n_pages) continue;
+    void *dh = nullptr, *dc = nullptr;
+    GRIT_CUDA(cudaMalloc(&dh, peers[r].n_pages * 8));
+    d_peer_bufs_.push_back(dh);
+    GRIT_CUDA(cudaMalloc(&dc, peers[r].n_pages * 4));
+    d_peer_bufs_.push_back(dc);
+    GRIT_CUDA(cudaMemcpyAsync(dh, peers[r].hash, peers[r].n_pages * 8, cudaMemcpyHostToDevice, s));
+    GRIT_CUDA(cudaMemcpyAsync(dc, peers[r].crc, peers[r].n_pages * 4, cudaMemcpyHostToDevice, s));
+    crcs_.peer[r] = static_cast<const uint32_t*>(dc);
+    h2d_bytes += peers[r].n_pages * 12.0;
+    GRIT_CUDA(launch_table_insert(ctx_->geom, table_, static_cast<const uint64_t*>(dh), nullptr, peers[r].n_pages, 1 + r, 0, s));
     ctx_->launches++;
   }
   return GRIT_OK;
@@ -235,7 +255,7 @@ int PackStream::finish(grit_pack_stats* stats, char* err, size_t errlen) {
 int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const uint32_t* h_ref,
                    const uint32_t* h_crc, uint64_t n_pages, const void* parent_image, uint64_t parent_pages,
                    bool parent_on_device, int verify, uint64_t chunk_pages, grit_restore_stats* stats,
-                   double* h2d_total, double* d2h_total, char* err, size_t errlen) {
+                   double* h2d_total, double* d2h_total, char* err, size_t errlen, const PeerImages* peers) {
   GRIT_CUDA(cudaSetDevice(ctx->device));
   if (n_pages > GRIT_MAX_PAGES) return fail(err, errlen, GRIT_EINVAL, "image exceeds GRIT_MAX_PAGES");
   chunk_pages = std::max<uint64_t>(chunk_pages, 256);
@@ -283,6 +303,9 @@ int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const u
     h2d += n_pages * 8.0;
   }
   PeerImages imgs{};
+  if (peers) imgs = *peers;
+  imgs.parent = nullptr;
+  imgs.parent_pages = 0;
   if (parent_image && parent_pages) {
     if (parent_on_device) {
       r.d_parent = const_cast<void*>(parent_image);

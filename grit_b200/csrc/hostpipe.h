@@ -24,7 +24,9 @@ class PackStream {
   PackStream(grit_ctx* ctx, uint64_t total_pages, uint64_t chunk_pages);
   ~PackStream();
   // parent: HOST arrays of the previous checkpoint's per-page hashes, or null
-  int begin(const grit_table* parent_host, char* err, size_t errlen);
+  // peers_host[0..n_peers): HOST tables of the ranks below this one
+  int begin(const grit_table* parent_host, char* err, size_t errlen, const grit_table* peers_host = nullptr,
+            uint32_t n_peers = 0);
   // pinned staging buffers, one per chunk in flight, for callers without pinned memory
   int alloc_staging(bool in, bool out, char* err, size_t errlen);
   // pinned staging buffer for chunk i (valid between submit-ready and the H2D of chunk i)
@@ -70,6 +72,7 @@ class PackStream {
   uint64_t* d_hash_ = nullptr;
   uint64_t* d_parent_hash_ = nullptr;
   uint32_t* d_parent_crc_ = nullptr;
+  std::vector<void*> d_peer_bufs_;  // peers' tables on the device (owned)
   uint64_t chunk_page0_[kPipeDepth] = {};
   DedupTable table_{};
   PeerCrcs crcs_{};
@@ -89,10 +92,11 @@ struct RestoreIO {
 
 // parent_image: the parent's fully restored image, in host memory (uploaded) or,
 // with parent_on_device, already on the context's device.
+// peers: restored images of lower ranks, already on the device (may be null)
 int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const uint32_t* h_ref,
                    const uint32_t* h_crc, uint64_t n_pages, const void* parent_image, uint64_t parent_pages,
                    bool parent_on_device, int verify, uint64_t chunk_pages, grit_restore_stats* stats,
-                   double* h2d_bytes, double* d2h_bytes, char* err, size_t errlen);
+                   double* h2d_bytes, double* d2h_bytes, char* err, size_t errlen, const PeerImages* peers = nullptr);
 
 bool is_pinned(const void* p);
 

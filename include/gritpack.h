@@ -80,6 +80,14 @@ typedef struct grit_opts {
   uint32_t io_threads;  /* file reader/writer threads, 0 = default (8)         */
   uint64_t chunk_bytes; /* pipeline chunk, 0 = default (64 MiB)                */
   const char *parent_dir; /* previous packed checkpoint for incremental, or NULL */
+  /* Cross-rank dedup of a multi-GPU job (grit_pack_dir only): the per-page tables
+   * of the ranks below this one, HOST pointers, as an all-gather of the ranks'
+   * K1 results or the lower ranks' hashes.bin / pagemap.bin provide them, and the
+   * directories those ranks pack into on the shared PV (recorded in the manifest
+   * so that grit_restore_dir can follow PEER references).  Lowest rank owns a page. */
+  uint32_t n_peers;              /* 0..GRIT_MAX_PEERS                              */
+  const grit_table *peer_tables; /* [n_peers]                                      */
+  const char *const *peer_dirs;  /* [n_peers]                                      */
 } grit_opts;
 
 typedef struct grit_stats {

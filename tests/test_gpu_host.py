@@ -207,3 +207,40 @@ def test_cpp_grit_agent_binary(oracle, tmp_path):
     assert tree_snapshot(str(host)) == tree_snapshot(str(src))
     r = subprocess.run([exe, "--action", "migrate"], capture_output=True, text=True)
     assert r.returncode == 1 and "run grit-agent failed: unknown action migrate" in r.stderr      # app.go:40,68
+
+
+def test_directory_cross_rank_peers(oracle, tmp_path):
+    """Three ranks of one job pack into a shared PV: replicated base weights are stored by rank 0 only, the others keep
+    PEER references (rank 2 also refers to pages only rank 1 holds), and every rank restores its own tree exactly."""
+    from grit_b200 import _lib, copy
+    shared = oracle.synth_image(3000, 0xBA5E, pct_zero=0, pct_dup=0).tobytes()
+    only_1_and_2 = oracle.synth_image(500, 0x12, pct_zero=0, pct_dup=0).tobytes()
+    srcs, pvs = [], []
+    for r in range(3):
+        src = tmp_path / f"host{r}" / "main" / "checkpoint"
+        src.mkdir(parents=True)
+        (src / "pages-1.img").write_bytes(shared)
+        (src / "pages-2.img").write_bytes(oracle.synth_image(400 + 50 * r, 100 + r, pct_zero=10, pct_dup=10, dup_pool=4).tobytes())
+        if r:
+            (src / "pages-3.img").write_bytes(only_1_and_2)
+        (src / "inventory.img").write_bytes(bytes([r]) * 77)
+        srcs.append(tmp_path / f"host{r}")
+        pvs.append(tmp_path / "pv" / f"ckpt-rank{r}")
+    stats = []
+    for r in range(3):
+        peers = [copy.read_tables(str(pvs[q])) + (str(pvs[q]),) for q in range(r)]
+        stats.append(copy.TransferData(str(srcs[r]), str(pvs[r]), copy.UPLOAD, peers=peers))
+    assert stats[0]["n_peer"] == 0
+    assert stats[1]["n_peer"] >= 3000 and stats[2]["n_peer"] >= 3500
+    assert stats[2]["n_data"] < 600
+    for r in range(3):
+        back = tmp_path / f"back{r}"
+        st = copy.TransferData(str(pvs[r]), str(back), copy.DOWNLOAD)
+        assert st["n_bad"] == 0 and st["n_peer"] == stats[r]["n_peer"]
+        assert tree_snapshot(str(back)) == tree_snapshot(str(srcs[r]))
+        assert copy.VerifyData(str(pvs[r]))["n_bad"] == 0
+    # without the lower ranks' directories the references cannot be followed
+    import shutil
+    shutil.rmtree(pvs[0])
+    with pytest.raises(_lib.GritError):
+        copy.TransferData(str(pvs[2]), str(tmp_path / "nope"), copy.DOWNLOAD)
