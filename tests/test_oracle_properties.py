@@ -37,3 +37,34 @@ def test_incremental_is_exact_for_any_dirty_set(n_pages, seed, dirty):
     out, bad, _ = O.restore(c["packed"], c["ref"], c["crc"], parent_image=base)
     assert bad == 0 and np.array_equal(out, child)
     assert c["stats"]["n_data"] <= len(set(x % n_pages for x in dirty))
+
+
+def test_hash64_is_position_and_bit_sensitive():
+    """hash64 keys the dedup table: a flipped bit anywhere, swapped segments, or a shifted page must change it
+    (collisions are still caught by the CRC-32C check, but the hash should not offer them cheaply)."""
+    rng = np.random.default_rng(7)
+    page = rng.integers(0, 256, PAGE, dtype=np.uint8)
+    h0 = O.hash64_page(page.tobytes())
+    seen = {h0}
+    for off in list(range(0, PAGE, 97)) + [0, 1, 15, 16, 127, 128, 4095]:
+        for bit in (0, 7):
+            q = page.copy()
+            q[off] ^= 1 << bit
+            h = O.hash64_page(q.tobytes())
+            assert h != h0
+            seen.add(h)
+    assert len(seen) > 80                          # all distinct from each other as well
+    for a, b in [(0, 1), (0, 8), (3, 200), (7, 255), (16, 24)]:   # swap two 16-byte segments
+        q = page.copy()
+        q[16 * a:16 * a + 16], q[16 * b:16 * b + 16] = page[16 * b:16 * b + 16], page[16 * a:16 * a + 16]
+        assert O.hash64_page(q.tobytes()) != h0
+    assert O.hash64_page(np.roll(page, 16).tobytes()) != h0
+    assert O.hash64_page(np.roll(page, 128).tobytes()) != h0
+    # structured pages that differ in one word only
+    base = np.zeros(PAGE, np.uint8)
+    hs = set()
+    for w in range(0, 1024, 3):
+        q = base.copy()
+        q[4 * w] = 1
+        hs.add(O.hash64_page(q.tobytes()))
+    assert len(hs) == len(range(0, 1024, 3))
