@@ -84,6 +84,7 @@ SYMBOLS = {
     "grit_pack_dir": (_I, [C.c_char_p, C.c_char_p, C.POINTER(Opts), C.POINTER(Stats)] + _ERR),
     "grit_restore_dir": (_I, [C.c_char_p, C.c_char_p, C.POINTER(Opts), C.POINTER(Stats)] + _ERR),
     "grit_verify_dir": (_I, [C.c_char_p, C.POINTER(Opts), C.POINTER(Stats)] + _ERR),
+    "grit_image_deps": (_I, [C.c_char_p, C.c_int, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t)] + _ERR),
     "grit_write_sentinel": (_I, [C.c_char_p, C.c_char_p]),
 }
 

@@ -71,6 +71,20 @@ def CreateSentinelFile(dir, file_name):
         raise GritError(rc, f"cannot create {os.path.join(dir, file_name)}")
 
 
+def ImageDependencies(packed_dir, recursive=True):
+    """The packed directories `packed_dir` needs in order to be restored (grit_image_deps): its parent and the lower
+    ranks its page map refers to, and with `recursive` what those need.  Host work only.  What a garbage collector
+    of old checkpoints on the PV consults before deleting one."""
+    lib = _lib.load()
+    need, err = C.c_size_t(0), _lib.errbuf()
+    rc = lib.grit_image_deps(os.fsencode(packed_dir), int(bool(recursive)), None, 0, C.byref(need), err, len(err))
+    if rc != _lib.EINVAL or need.value == 0:
+        _lib.check(rc, err)
+    buf = C.create_string_buffer(need.value)
+    _lib.check(lib.grit_image_deps(os.fsencode(packed_dir), int(bool(recursive)), buf, need.value, C.byref(need), err, len(err)), err)
+    return [os.fsdecode(x) for x in buf.raw[: need.value - 1].split(b"\0") if x]
+
+
 def VerifyData(packed_dir, **kw):
     """Checks a packed checkpoint on the PV without restoring it (grit_verify_dir): checksums of the metadata,
     CRC-32C of every stored page recomputed on the GPU.  Raises GritError (ECRC / EFORMAT) on damage."""

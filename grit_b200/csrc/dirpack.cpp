@@ -988,4 +988,41 @@ int grit_verify_dir(const char* src_dir, const grit_opts* opts, grit_stats* stat
   return restore_or_verify(src_dir, nullptr, opts, stats, err, errlen);
 }
 
+int grit_image_deps(const char* dir, int recursive, char* out, size_t outlen, size_t* needed, char* err, size_t errlen) {
+  if (!dir) return fail(err, errlen, GRIT_EINVAL, "null directory");
+  std::vector<std::string> deps, todo{dir};
+  std::string msg;
+  for (size_t i = 0; i < todo.size(); i++) {  // breadth first; todo[0] is the image itself
+    if (i > 0 && !recursive) break;
+    if (!has_manifest(todo[i]))
+      return fail(err, errlen, GRIT_EFORMAT, "%s holds no %s: not a complete gritpack image", todo[i].c_str(), kManifest);
+    Manifest m;
+    if (int rc = load_manifest(todo[i], &m, &msg)) return fail(err, errlen, rc, "%s", msg.c_str());
+    std::vector<uint32_t> ref, crc;
+    if (int rc = load_pagemap(todo[i], m, &ref, &crc, &msg)) return fail(err, errlen, rc, "%s", msg.c_str());
+    bool used[GRIT_MAX_PEERS] = {};
+    if (int rc = peers_used(m, ref, used, &msg)) return fail(err, errlen, rc, "%s: %s", todo[i].c_str(), msg.c_str());
+    auto add = [&](const std::string& d) {
+      const std::string r = resolve_parent(todo[i], d);
+      if (r == todo[0] || std::find(deps.begin(), deps.end(), r) != deps.end()) return;
+      deps.push_back(r);
+      todo.push_back(r);
+    };
+    if (!m.parent.empty()) add(m.parent);  // grit_restore_dir loads the parent whenever one is named
+    for (uint32_t r = 0; r < m.peers.size(); r++)
+      if (used[r]) add(m.peers[r]);
+  }
+  size_t need = 1;
+  for (const auto& d : deps) need += d.size() + 1;
+  if (needed) *needed = need;
+  if (!out || outlen < need) return fail(err, errlen, GRIT_EINVAL, "dependency list needs %zu bytes", need);
+  char* w = out;
+  for (const auto& d : deps) {
+    memcpy(w, d.c_str(), d.size() + 1);
+    w += d.size() + 1;
+  }
+  *w = 0;
+  return GRIT_OK;
+}
+
 }  // extern "C"

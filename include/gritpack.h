@@ -258,8 +258,10 @@ int grit_pack_dir(const char *src_dir, const char *dst_dir,
 /* Download direction of TransferData (restore.go:16): recreates under dst_dir
  * the tree grit_pack_dir saw -- same relative paths, file bytes and mode bits,
  * directories 0777 & ~umask (copy.go:36,84-89).  A src_dir without a gritpack
- * manifest (written by the stock agent) is mirrored file by file.  Does not
- * write the sentinel. */
+ * manifest (a plain mirror uploaded by the stock agent, or a pack that did not
+ * finish) is refused with GRIT_EFORMAT and nothing is written: the caller hands
+ * plain mirrors to the stock TransferData (integration/copy_gritpack.go does).
+ * Does not write the sentinel. */
 int grit_restore_dir(const char *src_dir, const char *dst_dir,
                      const grit_opts *opts, grit_stats *stats, char *err,
                      size_t errlen);
@@ -272,6 +274,19 @@ int grit_restore_dir(const char *src_dir, const char *dst_dir,
  * step of SURVEY 8(f). */
 int grit_verify_dir(const char *src_dir, const grit_opts *opts,
                     grit_stats *stats, char *err, size_t errlen);
+
+/* Which other packed directories a packed directory needs in order to be
+ * restored: its parent (the previous checkpoint of an incremental chain) and
+ * the lower ranks its page map refers to, resolved the way grit_restore_dir
+ * resolves them; with recursive != 0 also what those need, each directory once.
+ * Host work only (manifests and page maps are read, no GPU is touched).  The
+ * list is written to out as NUL-terminated paths followed by an empty string;
+ * *needed receives the bytes that takes, and GRIT_EINVAL is returned (nothing
+ * written) when outlen is smaller.  This is what a garbage collector of old
+ * checkpoints consults before deleting a directory from the PV;
+ * the reference never deletes or links checkpoints, so there is no counterpart. */
+int grit_image_deps(const char *dir, int recursive, char *out, size_t outlen,
+                    size_t *needed, char *err, size_t errlen);
 
 /* CreateSentinelFile (copy.go:92-102): dir/name holding "Transfer Completed\n". */
 int grit_write_sentinel(const char *dir, const char *name);

@@ -20,6 +20,7 @@ import (
 	"context"
 	"errors"
 	"os"
+	"path/filepath"
 	"unsafe"
 
 	"sigs.k8s.io/controller-runtime/pkg/log"
@@ -70,8 +71,13 @@ func TransferDataUpload(ctx context.Context, srcDir, dstDir string) error {
 	return transfer(ctx, Upload, srcDir, dstDir)
 }
 
-// TransferDataDownload replaces copy.TransferData at restore.go:16.
+// TransferDataDownload replaces copy.TransferData at restore.go:16.  A checkpoint that the stock agent
+// uploaded is a plain mirror without a manifest; grit_restore_dir refuses it (GRIT_EFORMAT), so it goes
+// through the stock TransferData of copy.go, which stays in this package.
 func TransferDataDownload(ctx context.Context, srcDir, dstDir string) error {
+	if _, err := os.Stat(filepath.Join(srcDir, "gritpack.manifest")); os.IsNotExist(err) {
+		return TransferData(ctx, srcDir, dstDir)
+	}
 	return transfer(ctx, Download, srcDir, dstDir)
 }
 

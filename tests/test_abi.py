@@ -58,6 +58,16 @@ def test_sentinel_matches_reference_payload(tmp_path):
         copy.CreateSentinelFile(str(tmp_path / "missing"), "download-state")
 
 
+def test_image_deps_refuses_a_plain_mirror(tmp_path):
+    """grit_image_deps is host work: on a directory the stock agent wrote (no manifest) it says so, like restore."""
+    from grit_b200 import _lib, copy
+    (tmp_path / "checkpoint").mkdir()
+    (tmp_path / "checkpoint" / "pages-1.img").write_bytes(b"\0" * 4096)
+    with pytest.raises(_lib.GritError) as e:
+        copy.ImageDependencies(str(tmp_path))
+    assert e.value.code == _lib.EFORMAT and "gritpack.manifest" in e.value.message
+
+
 def test_no_cpu_fallback_without_a_device():
     """Without a usable GPU the product must fail loudly, never compute on the CPU."""
     import torch

@@ -106,6 +106,12 @@ def test_directory_incremental_and_rerun(oracle, tmp_path):
     assert st_again["n_data"] == st["n_data"]
     copy.TransferData(str(pv2), str(host), copy.DOWNLOAD)
     assert tree_snapshot(str(host)) == tree_snapshot(str(src))
+    # a chain: c3 on c2 on c1; deleting c1 or c2 from the PV would break c3
+    pv3 = tmp_path / "pv/c3"
+    copy.TransferData(str(src), str(pv3), copy.UPLOAD, parent_dir=str(pv2))
+    assert copy.ImageDependencies(str(pv3), recursive=False) == [str(pv2)]
+    assert copy.ImageDependencies(str(pv3)) == [str(pv2), str(pv1)]
+    assert copy.ImageDependencies(str(pv1)) == []
 
 
 def test_restore_dir_refuses_incomplete_or_corrupt_images(oracle, tmp_path):
@@ -239,8 +245,15 @@ def test_directory_cross_rank_peers(oracle, tmp_path):
         assert st["n_bad"] == 0 and st["n_peer"] == stats[r]["n_peer"]
         assert tree_snapshot(str(back)) == tree_snapshot(str(srcs[r]))
         assert copy.VerifyData(str(pvs[r]))["n_bad"] == 0
+    # what a garbage collector of the PV must keep: rank 2 needs ranks 0 and 1, rank 1 needs rank 0
+    assert copy.ImageDependencies(str(pvs[0])) == []
+    assert copy.ImageDependencies(str(pvs[1])) == [str(pvs[0])]
+    assert sorted(copy.ImageDependencies(str(pvs[2]), recursive=False)) == sorted([str(pvs[0]), str(pvs[1])])
     # without the lower ranks' directories the references cannot be followed
     import shutil
     shutil.rmtree(pvs[0])
+    with pytest.raises(_lib.GritError):
+        copy.ImageDependencies(str(pvs[2]))
+    assert str(pvs[0]) in copy.ImageDependencies(str(pvs[2]), recursive=False)      # named, though gone
     with pytest.raises(_lib.GritError):
         copy.TransferData(str(pvs[2]), str(tmp_path / "nope"), copy.DOWNLOAD)
