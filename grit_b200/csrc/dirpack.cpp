@@ -273,6 +273,17 @@ int load_manifest(const std::string& dir, Manifest* m, std::string* msg) {
     m->entries.push_back(std::move(e));
   }
   if (!r.ok || r.off + 4 != b.size() || m->n_pages > GRIT_MAX_PAGES) return *msg = dir + ": truncated manifest", GRIT_EFORMAT;
+  // the files tile the page stream in manifest order, without gaps or overlap (how grit_pack_dir numbers them)
+  uint64_t next_page = 0, bytes = 0;
+  for (const auto& e : m->entries) {
+    if (e.type > 1) return *msg = dir + ": manifest holds an unknown entry type", GRIT_EFORMAT;
+    if (e.type == 0) continue;
+    if (e.first_page != next_page || e.size > (uint64_t)GRIT_MAX_PAGES * kPage) return *msg = dir + ": manifest entries do not tile the image", GRIT_EFORMAT;
+    next_page += e.pages();
+    bytes += e.size;
+  }
+  if (next_page != m->n_pages || bytes != m->bytes_logical || m->n_slots > m->n_pages)
+    return *msg = dir + ": manifest totals do not match its entries", GRIT_EFORMAT;
   return GRIT_OK;
 }
 
