@@ -345,6 +345,7 @@ int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const u
     uint64_t written = 0;
     int rc = 0;
     bool stop = false;
+    double t_read = 0, t_write = 0, t_write_wait = 0, t_main_wait_read = 0, t_main_wait_write = 0;  // GRITPACK_DEBUG
     std::thread reader, writer;
     ~Helpers() {
       {
@@ -369,7 +370,9 @@ int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const u
           cudaEventSynchronize(r.ev_stage[b]);
         }
         const uint64_t s0 = c * chunk_pages, n = std::min(chunk_pages, n_slots - s0);
+        const double t0 = wall();
         const int rc = io.read_packed(s0, n, r.h_stage_in[b]);
+        hp.t_read += wall() - t0;
         std::lock_guard<std::mutex> l(hp.mu);
         if (rc && !hp.rc) hp.rc = rc;
         hp.filled = c + 1;
@@ -389,8 +392,12 @@ int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const u
           j = hp.jobs.front();
           hp.jobs.pop_front();
         }
+        const double t0 = wall();
         int rc = cudaEventSynchronize(r.ev_d2h[j.b]) == cudaSuccess ? 0 : GRIT_ECUDA;
+        const double t1 = wall();
         if (!rc) rc = io.write_out(j.p0, j.p1, r.h_stage_out[j.b]);
+        hp.t_write_wait += t1 - t0;
+        hp.t_write += wall() - t1;
         std::lock_guard<std::mutex> l(hp.mu);
         if (rc && !hp.rc) hp.rc = rc;
         hp.written++;
@@ -406,8 +413,10 @@ int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const u
       const char* src = static_cast<const char*>(h_packed) + s0 * kPage;
       const int b = (int)(uploaded % kStageIn);
       if (!in_pinned) {  // no pinned source: the reader thread fills pinned staging
+        const double t0 = wall();
         std::unique_lock<std::mutex> l(hp.mu);
         hp.cv.wait(l, [&] { return hp.rc || hp.filled > uploaded; });
+        hp.t_main_wait_read += wall() - t0;
         if (hp.rc) return fail(err, errlen, hp.rc, "reading packed pages failed");
         src = static_cast<const char*>(r.h_stage_in[b]);
       }
@@ -444,8 +453,10 @@ int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const u
     char* dst = static_cast<char*>(h_out) + p0 * kPage;
     if (!out_pinned) {
       if (i >= (uint64_t)kPipeDepth) {  // staging buffer b still holds chunk i - depth until the writer is done with it
+        const double t0 = wall();
         std::unique_lock<std::mutex> l(hp.mu);
         hp.cv.wait(l, [&] { return hp.rc || hp.written > i - kPipeDepth; });
+        hp.t_main_wait_write += wall() - t0;
         if (hp.rc) return fail(err, errlen, hp.rc, "writing restored pages failed");
       }
       dst = static_cast<char*>(r.h_stage_out[b]);
@@ -472,8 +483,11 @@ int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const u
   if (h2d_total) *h2d_total += h2d;
   if (d2h_total) *d2h_total += d2h;
   if (debug_on())
-    fprintf(stderr, "[gritpack] restore_stream: alloc %.1f ms, stream %.1f ms\n", (t_loop - t_begin) * 1e3,
-            (wall() - t_loop) * 1e3);
+    fprintf(stderr,
+            "[gritpack] restore_stream: alloc %.1f ms, stream %.1f ms (reader busy %.1f, writer busy %.1f + %.1f waiting for "
+            "the D2H, main thread waited %.1f for the reader and %.1f for the writer)\n",
+            (t_loop - t_begin) * 1e3, (wall() - t_loop) * 1e3, hp.t_read * 1e3, hp.t_write * 1e3, hp.t_write_wait * 1e3,
+            hp.t_main_wait_read * 1e3, hp.t_main_wait_write * 1e3);
   const DevCounters& c = *ctx->h_cnt;
   if (stats) {
     stats->n_pages = n_pages;

@@ -14,8 +14,12 @@ def u32(t):
     return t.numpy().view(np.uint32)
 
 
-def read_page_store(pv, n_slots, k=8, stripe=2048):
-    """The stored pages in slot order, reassembled from the striped pages-NNN.bin files."""
+def read_page_store(pv, n_slots):
+    """The stored pages in slot order, reassembled from the striped pages-NNN.bin files (shard count and stripe
+    length are manifest fields)."""
+    import struct
+    with open(os.path.join(pv, "gritpack.manifest"), "rb") as f:
+        k, stripe = struct.unpack_from("<II", f.read(), 48)
     shards = [np.fromfile(os.path.join(pv, f"pages-{i:03d}.bin"), np.uint8) for i in range(k)]
     out = np.empty(n_slots * PAGE, np.uint8)
     for t in range((n_slots + stripe - 1) // stripe):

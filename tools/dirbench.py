@@ -22,17 +22,24 @@ try:
     os.makedirs(src)
     total = build_c1_tree(src, O)
     extra_gib = int(os.environ.get("DIRBENCH_EXTRA_GIB", "0"))   # a bigger image: one more pages-N.img per GiB
-    for k in range(extra_gib):
-        with open(os.path.join(src, "main", "checkpoint", f"pages-{10 + k}.img"), "wb") as f:
+    one_file = bool(os.environ.get("DIRBENCH_ONE_FILE"))       # ... or all of it appended to one file (the usual
+    for k in range(extra_gib):                                   # CRIU image: one giant pages-1.img)
+        name = "pages-10.img" if one_file else f"pages-{10 + k}.img"
+        with open(os.path.join(src, "main", "checkpoint", name), "ab" if one_file else "wb") as f:
             f.write(O.synth_image((1 << 30) // 4096, 777 + k, 10, 15, 1024).tobytes())
         total += 1 << 30
-    res = {"tree_bytes": total}
+    kw = {}
+    if os.environ.get("DIRBENCH_CHUNK_MB"):                      # chunk size of the host pipeline (default: by image size)
+        kw["chunk_bytes"] = int(os.environ["DIRBENCH_CHUNK_MB"]) << 20
+    if os.environ.get("DIRBENCH_IO_THREADS"):
+        kw["io_threads"] = int(os.environ["DIRBENCH_IO_THREADS"])
+    res = {"tree_bytes": total, "options": kw}
     for rep in range(3):
         pv, back = os.path.join(base, "pv"), os.path.join(base, "back")
         t0 = time.perf_counter()
-        st = copy.TransferData(src, pv, copy.UPLOAD)
+        st = copy.TransferData(src, pv, copy.UPLOAD, **kw)
         t1 = time.perf_counter()
-        st2 = copy.TransferData(pv, back, copy.DOWNLOAD)
+        st2 = copy.TransferData(pv, back, copy.DOWNLOAD, **kw)
         copy.CreateSentinelFile(back, "download-state")
         t2 = time.perf_counter()
         res[f"gritpack_{rep}"] = {"pack_s": round(t1 - t0, 3), "restore_s": round(t2 - t1, 3),
