@@ -9,7 +9,7 @@
 // becomes one page stream -- every regular file, in filepath.WalkDir order
 // (copy.go:23), padded with zeros to a 4 KiB multiple -- that goes through the
 // GPU pack pipeline; the PV receives
-//     pages-NNN.bin      the pages that had to be stored: slot order, striped 8 MiB-wise over 8 files
+//     pages-NNN.bin      the pages that had to be stored: slot order, striped 1-8 MiB-wise over 8 files
 //                        (a file system takes one writer per file; eight files take eight)
 //     pagemap.bin        u32 ref[n_pages] then u32 crc32c[n_pages]
 //     hashes.bin         u64 hash64[n_pages]   (input of the next incremental pack)
