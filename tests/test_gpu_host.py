@@ -5,6 +5,7 @@ import numpy as np
 import pytest
 import torch
 
+from golden_dir import PackedDir
 from helpers import PAGE, make_criu_tree, mixed_image, tree_snapshot
 
 pytestmark = pytest.mark.gpu
@@ -90,6 +91,38 @@ def test_directory_round_trip_equals_reference_copy(oracle, tmp_path):
     assert oracle.create_sentinel_file(str(ref_host), "download-state") == 0
     assert tree_snapshot(str(host)) == tree_snapshot(str(ref_host))
     assert (host / "download-state").read_bytes() == b"Transfer Completed\n"
+
+
+@pytest.mark.parametrize("chunk_mb,io_threads,no_mmap", [(1, 1, False), (1, 5, True), (2, 16, False), (0, 3, False)])
+def test_directory_options_do_not_change_the_result(oracle, tmp_path, monkeypatch, chunk_mb, io_threads, no_mmap):
+    """Chunk size (hence piece and stripe size), the number of I/O threads and the write path of the destination are
+    performance knobs: page map, stored pages and the restored tree are the same for every setting."""
+    from grit_b200 import copy
+    if no_mmap:
+        monkeypatch.setenv("GRITPACK_NO_MMAP", "1")
+    base = "/dev/shm" if os.path.isdir("/dev/shm") else str(tmp_path)      # tmpfs: the mapped write path
+    root = os.path.join(base, f"grit_opts_{os.getpid()}_{chunk_mb}_{io_threads}")
+    import shutil
+    try:
+        src, pv, host = (os.path.join(root, n) for n in ("src", "pv", "host"))
+        os.makedirs(src)
+        make_criu_tree(src, oracle, big_pages=5000)
+        kw = dict(chunk_bytes=chunk_mb << 20, io_threads=io_threads)
+        st = copy.TransferData(src, pv, copy.UPLOAD, **kw)
+        stream = bytearray()
+        for typ, _, _, _, path in PackedDir(pv, oracle.crc32c).entries:
+            if typ == 1:
+                b = open(os.path.join(src, path), "rb").read()
+                stream += b + bytes(-len(b) % PAGE)
+        o = oracle.pack(np.frombuffer(bytes(stream), np.uint8), threads=8)
+        assert {k: st[k] for k in o["stats"]} == o["stats"]
+        pm = np.fromfile(os.path.join(pv, "pagemap.bin"), np.uint32)
+        assert np.array_equal(pm[: o["ref"].size], o["ref"]) and np.array_equal(pm[o["ref"].size:], o["crc"])
+        assert np.array_equal(read_page_store(pv, o["stats"]["n_data"]), o["packed"])
+        assert copy.TransferData(pv, host, copy.DOWNLOAD, **kw)["n_bad"] == 0
+        assert tree_snapshot(host) == tree_snapshot(src)
+    finally:
+        shutil.rmtree(root, ignore_errors=True)
 
 
 def test_directory_incremental_and_rerun(oracle, tmp_path):
