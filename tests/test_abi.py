@@ -58,6 +58,20 @@ def test_sentinel_matches_reference_payload(tmp_path):
         copy.CreateSentinelFile(str(tmp_path / "missing"), "download-state")
 
 
+def test_cgo_stub_is_documented_and_binds_exported_symbols():
+    """The stub a maintainer drops into pkg/gritagent/copy is printed in INTEGRATION.md as it is in integration/, and
+    every C function it calls is one the library exports (no Go toolchain here to compile it)."""
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    stub = open(os.path.join(root, "integration", "copy_gritpack.go")).read()
+    doc = open(os.path.join(root, "INTEGRATION.md")).read()
+    assert stub.strip() in doc
+    called = set(re.findall(r"C\.(grit_[a-z0-9_]+)\(", stub))
+    assert called >= {"grit_pack_dir", "grit_restore_dir", "grit_write_sentinel"}
+    lib = _lib.load()
+    for name in called:
+        assert hasattr(lib, name), name
+
+
 def test_image_deps_refuses_a_plain_mirror(tmp_path):
     """grit_image_deps is host work: on a directory the stock agent wrote (no manifest) it says so, like restore."""
     from grit_b200 import _lib, copy
