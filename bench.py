@@ -220,6 +220,9 @@ def run_gritpack(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     if world > 1:
+        # stdout carries the one JSON line: whatever NCCL has to say (its version banner at NCCL_DEBUG=VERSION,
+        # the NVLS lines at INFO) goes to stderr
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     ctx = Context(local)
     dev = torch.device("cuda", local)
