@@ -205,7 +205,7 @@ def run_reference(args):
         "e2e": {"value": round(gbs, 4), "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    print(json.dumps(line), file=RESULT, flush=True)
     return 0
 
 
@@ -220,9 +220,6 @@ def run_gritpack(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     if world > 1:
-        # stdout carries the one JSON line: whatever NCCL has to say (its version banner at NCCL_DEBUG=VERSION,
-        # the NVLS lines at INFO) goes to stderr
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     ctx = Context(local)
     dev = torch.device("cuda", local)
@@ -512,13 +509,22 @@ def run_gritpack(args):
             "gpu_launches": int(launches),
             "clocks": clocks, "bit_exact": True,
         }
-        print(json.dumps(line))
+        print(json.dumps(line), file=RESULT, flush=True)
     if world > 1:
         dist.destroy_process_group()
     return 0
 
 
+RESULT = sys.stdout
+
+
 def main():
+    # stdout carries the one JSON line and nothing else: native libraries print there too (NCCL's version banner
+    # does), so file descriptor 1 is pointed at stderr for the run and the result goes to a private copy of it
+    global RESULT
+    sys.stdout.flush()
+    RESULT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=40)
