@@ -82,6 +82,24 @@ def test_image_deps_refuses_a_plain_mirror(tmp_path):
     assert e.value.code == _lib.EFORMAT and "gritpack.manifest" in e.value.message
 
 
+def test_directory_calls_check_their_arguments_before_touching_the_gpu(tmp_path):
+    """What can be refused on the host is refused there, with the reference's kind of message (copy.go:24-26 returns
+    the walk error): a source that is not a directory, a download source that holds no packed image."""
+    from grit_b200 import copy
+    with pytest.raises(_lib.GritError) as e:
+        copy.TransferData(str(tmp_path / "missing"), str(tmp_path / "pv"), copy.UPLOAD)
+    assert e.value.code == _lib.EIO and "not a directory" in e.value.message
+    assert not (tmp_path / "pv").exists()
+    (tmp_path / "plain").mkdir()
+    (tmp_path / "plain" / "a.img").write_bytes(b"x" * 10)
+    with pytest.raises(_lib.GritError) as e:
+        copy.TransferData(str(tmp_path / "plain"), str(tmp_path / "host"), copy.DOWNLOAD)
+    assert e.value.code == _lib.EFORMAT and not (tmp_path / "host").exists()
+    with pytest.raises(_lib.GritError) as e:
+        copy.VerifyData(str(tmp_path / "plain"))
+    assert e.value.code == _lib.EFORMAT
+
+
 def test_no_cpu_fallback_without_a_device():
     """Without a usable GPU the product must fail loudly, never compute on the CPU."""
     import torch
