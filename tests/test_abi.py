@@ -100,6 +100,20 @@ def test_directory_calls_check_their_arguments_before_touching_the_gpu(tmp_path)
     assert e.value.code == _lib.EFORMAT
 
 
+def test_agent_mirrors_refuse_an_unknown_action(capsys, monkeypatch):
+    """cmd/grit-agent/app/app.go:39-42,66-68: "run grit-agent failed: unknown action X" on stderr, non-zero exit; the
+    action falls back to $ACTION (options.go:49).  Both mirrors, no GPU involved."""
+    import subprocess
+    from grit_b200 import agent
+    assert agent.main(["--action", "migrate"]) == 1
+    assert "run grit-agent failed: unknown action migrate" in capsys.readouterr().err
+    monkeypatch.setenv("ACTION", "snapshot")
+    exe = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "grit_b200", "csrc", "grit-agent")
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 1 and "run grit-agent failed: unknown action snapshot" in r.stderr
+    assert (agent.DownloadSentinelFile, agent.ContainerLogFile) == ("download-state", "container.log")   # metadata.go:8-9
+
+
 def test_no_cpu_fallback_without_a_device():
     """Without a usable GPU the product must fail loudly, never compute on the CPU."""
     import torch
