@@ -164,15 +164,24 @@ int dedup_async(grit_ctx* ctx, uint64_t n_pages, const uint32_t* d_crc, const ui
   }
   GRIT_CUDA(launch_table_insert(ctx->geom, t, d_hash, d_ref, n_pages, kOriginSelf, 0, s));
   ctx->launches++;
+  // the parent's and the lower ranks' hashes probe the table in one launch
+  ProbeLists lists{};
+  bool any = false;
   if (parent_on) {
-    GRIT_CUDA(launch_table_probe(ctx->geom, t, parent->hash, parent->n_pages, 0, s));
-    ctx->launches++;
+    lists.hash[0] = reinterpret_cast<const unsigned long long*>(parent->hash);
+    lists.n[0] = parent->n_pages;
+    any = true;
   }
   for (uint32_t r = 0; r < n_peers; r++)
     if (peers[r].n_pages) {
-      GRIT_CUDA(launch_table_probe(ctx->geom, t, peers[r].hash, peers[r].n_pages, 1 + r, s));
-      ctx->launches++;
+      lists.hash[1 + r] = reinterpret_cast<const unsigned long long*>(peers[r].hash);
+      lists.n[1 + r] = peers[r].n_pages;
+      any = true;
     }
+  if (any) {
+    GRIT_CUDA(launch_table_probe_lists(ctx->geom, t, lists, s));
+    ctx->launches++;
+  }
   GRIT_CUDA(launch_resolve(ctx->geom, t, 0, n_pages, d_crc, d_hash, d_ref, crcs, s));
   ctx->launches++;
   return GRIT_OK;

@@ -433,8 +433,12 @@ k_table_insert(DedupTable t, const unsigned long long* __restrict__ hash, const 
 
 // Other images' hashes against a table that already holds this image's: a hit lowers the owner,
 // a miss touches nothing, so the table stays the size of this image however many peers there are.
+// The parent and every lower rank are probed in one launch: blockIdx.y is the origin.
 __global__ void __launch_bounds__(256)
-k_table_probe(DedupTable t, const unsigned long long* __restrict__ hash, uint64_t n, uint32_t origin) {
+k_table_probe_lists(DedupTable t, ProbeLists lists) {
+  const uint32_t origin = blockIdx.y;
+  const unsigned long long* __restrict__ hash = lists.hash[origin];
+  const uint64_t n = lists.n[origin];
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
        i += (uint64_t)gridDim.x * blockDim.x) {
     const unsigned long long h = hash[i];
@@ -1059,10 +1063,12 @@ cudaError_t launch_table_insert(const LaunchGeom& g, DedupTable t, const uint64_
   return cudaGetLastError();
 }
 
-cudaError_t launch_table_probe(const LaunchGeom& g, DedupTable t, const uint64_t* d_hash, uint64_t n, uint32_t origin,
-                               cudaStream_t s) {
-  if (!n) return cudaSuccess;
-  k_table_probe<<<grid_for(g, n, 256, 8), 256, 0, s>>>(t, reinterpret_cast<const unsigned long long*>(d_hash), n, origin);
+cudaError_t launch_table_probe_lists(const LaunchGeom& g, DedupTable t, const ProbeLists& lists, cudaStream_t s) {
+  uint64_t longest = 0;
+  for (int o = 0; o < 9; o++) longest = std::max(longest, lists.n[o]);
+  if (!longest) return cudaSuccess;
+  dim3 grid(grid_for(g, longest, 256, 8), 9);  // an origin without a list costs a few empty blocks
+  k_table_probe_lists<<<grid, 256, 0, s>>>(t, lists);
   return cudaGetLastError();
 }
 

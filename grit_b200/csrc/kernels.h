@@ -27,6 +27,12 @@ struct PeerCrcs {
   const uint32_t* peer[8];
 };
 
+// the hash lists of the images a pack may refer to, probed against this image's table in one launch
+struct ProbeLists {
+  const unsigned long long* hash[9];  // [0] parent, [1 + r] rank r
+  uint64_t n[9];
+};
+
 struct PeerImages {
   const unsigned char* parent;
   uint64_t parent_pages;
@@ -65,8 +71,7 @@ cudaError_t launch_analyze(const LaunchGeom& g, const Gf2Tables* d_tab, const vo
 cudaError_t launch_table_insert(const LaunchGeom& g, DedupTable t, const uint64_t* d_hash,
                                 const uint32_t* d_ref_or_null, uint64_t n, uint32_t origin,
                                 uint64_t index_base, cudaStream_t s);
-cudaError_t launch_table_probe(const LaunchGeom& g, DedupTable t, const uint64_t* d_hash, uint64_t n, uint32_t origin,
-                               cudaStream_t s);
+cudaError_t launch_table_probe_lists(const LaunchGeom& g, DedupTable t, const ProbeLists& lists, cudaStream_t s);
 cudaError_t launch_resolve(const LaunchGeom& g, DedupTable t, uint64_t page0, uint64_t page1, const uint32_t* d_crc,
                            const uint64_t* d_hash, uint32_t* d_ref, PeerCrcs crcs, cudaStream_t s);
 cudaError_t launch_compact(const LaunchGeom& g, const void* d_image, uint64_t n_pages, uint32_t* d_ref,

@@ -33,11 +33,13 @@ def all_gather_tables(h, crc, group=None, counts=None):
         out[: t.numel()] = t
         return out
 
-    hs = [torch.empty(m, dtype=h.dtype, device=h.device) for _ in range(world)]
-    cs = [torch.empty(m, dtype=crc.dtype, device=crc.device) for _ in range(world)]
-    dist.all_gather(hs, padded(h), group=group)
-    dist.all_gather(cs, padded(crc), group=group)
-    return [(hs[r][: counts[r]], cs[r][: counts[r]]) for r in range(world)]
+    # one flat receive buffer per array: the collective writes every rank's block where it stays (a list of
+    # output tensors makes the NCCL backend gather into a scratch buffer and copy each block out afterwards)
+    hs = torch.empty(world * m, dtype=h.dtype, device=h.device)
+    cs = torch.empty(world * m, dtype=crc.dtype, device=crc.device)
+    dist.all_gather_into_tensor(hs, padded(h), group=group)
+    dist.all_gather_into_tensor(cs, padded(crc), group=group)
+    return [(hs[r * m: r * m + counts[r]], cs[r * m: r * m + counts[r]]) for r in range(world)]
 
 
 def peers_of(rank, tables):
