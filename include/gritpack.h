@@ -78,7 +78,7 @@ typedef struct grit_opts {
   int32_t device;       /* CUDA device ordinal                                 */
   uint32_t verify;      /* restore: recompute and compare every page's CRC-32C */
   uint32_t io_threads;  /* file reader/writer threads, 0 = default (8)         */
-  uint64_t chunk_bytes; /* pipeline chunk, 0 = default (64 MiB)                */
+  uint64_t chunk_bytes; /* pipeline chunk, 0 = by image size (4..16 MiB)      */
   const char *parent_dir; /* previous packed checkpoint for incremental, or NULL */
   /* Cross-rank dedup of a multi-GPU job (grit_pack_dir only): the per-page tables
    * of the ranks below this one, HOST pointers, as an all-gather of the ranks'
