@@ -111,12 +111,89 @@ def trial(ctx, rng, stats):
         stats["damage"] += 1
 
 
+def dir_trial(rng, stats, root):
+    """A random tree through grit_pack_dir / grit_verify_dir / grit_restore_dir with random performance options,
+    against the page stream packed by the oracle and the tree itself; every other trial packs a changed copy of the
+    tree against the first as its parent."""
+    import shutil
+    from grit_b200 import copy
+    from helpers import tree_snapshot
+    shutil.rmtree(root, ignore_errors=True)
+    src, pv, pv2, back = (os.path.join(root, n) for n in ("src", "pv", "pv2", "back"))
+    pool = rng.integers(0, 256, (8, PAGE), dtype=np.uint8)
+    names = []
+    for d in range(int(rng.integers(1, 4))):
+        sub = os.path.join(src, *[f"d{rng.integers(3)}" for _ in range(int(rng.integers(0, 3)))])
+        os.makedirs(sub, exist_ok=True)
+        for f in range(int(rng.integers(0, 5))):
+            size = int(rng.choice([0, 1, 4095, 4096, 4097, int(rng.integers(1, 70000)), PAGE * int(rng.integers(1, 9000))]))
+            data = random_image(rng, (size + PAGE - 1) // PAGE, pool)[:size] if size else np.empty(0, np.uint8)
+            path = os.path.join(sub, f"f{d}_{f}.img")
+            data.tofile(path)
+            os.chmod(path, int(rng.choice([0o600, 0o644, 0o444, 0o755])))
+            names.append(path)
+    kw = dict(chunk_bytes=int(rng.choice([0, 1, 2, 5])) << 20, io_threads=int(rng.integers(1, 13)))
+    st = copy.TransferData(src, pv, copy.UPLOAD, **kw)
+    assert copy.VerifyData(pv, **kw)["n_bad"] == 0, "verify"
+    rs = copy.TransferData(pv, back, copy.DOWNLOAD, **kw)
+    assert rs["n_bad"] == 0 and tree_snapshot(back) == tree_snapshot(src), "tree"
+    h, crc = copy.read_tables(pv)
+    if st["n_pages"]:
+        from golden_dir import PackedDir
+        stream = bytearray()
+        for typ, _, _, _, path in PackedDir(pv, O.crc32c).entries:
+            if typ == 1:
+                b = open(os.path.join(src, path), "rb").read()
+                stream += b + bytes(-len(b) % PAGE)
+        o = O.pack(np.frombuffer(bytes(stream), np.uint8))
+        pm = np.fromfile(os.path.join(pv, "pagemap.bin"), np.uint32)
+        assert np.array_equal(pm[: o["ref"].size], o["ref"]) and np.array_equal(pm[o["ref"].size:], o["crc"]), "page map"
+        assert np.array_equal(np.asarray(h).view(np.uint64), o["hash"]), "hashes"
+    if names and rng.random() < 0.5:                      # incremental: change a few bytes, pack against pv
+        victim = names[int(rng.integers(len(names)))]
+        size = os.path.getsize(victim)
+        if size:
+            os.chmod(victim, 0o600)
+            with open(victim, "r+b") as f:
+                for _ in range(3):
+                    f.seek(int(rng.integers(size)))
+                    f.write(bytes([int(rng.integers(256))]))
+        st2 = copy.TransferData(src, pv2, copy.UPLOAD, parent_dir=pv, **kw)
+        assert st2["n_data"] <= 3 + st["n_files"], ("incremental stores too much", st2["n_data"])
+        shutil.rmtree(back)
+        copy.TransferData(pv2, back, copy.DOWNLOAD, **kw)
+        assert tree_snapshot(back) == tree_snapshot(src), "incremental tree"
+        assert copy.ImageDependencies(pv2) == [pv], "deps"
+        stats["incremental"] += 1
+    stats["dirs"] += 1
+    stats["pages"] += st["n_pages"]
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--seconds", type=float, default=120)
     ap.add_argument("--seed", type=int, default=1)
+    ap.add_argument("--dirs", action="store_true", help="random directory trees through the directory calls instead")
     a = ap.parse_args()
     rng = np.random.default_rng(a.seed)
+    if a.dirs:
+        import tempfile
+        stats = dict(dirs=0, incremental=0, pages=0)
+        base = tempfile.mkdtemp(prefix="gritsoak_", dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
+        t0, i = time.time(), 0
+        try:
+            while time.time() - t0 < a.seconds:
+                try:
+                    dir_trial(rng, stats, os.path.join(base, "t"))
+                except AssertionError as e:
+                    print(json.dumps({"failed_trial": i, "seed": a.seed, "what": str(e), **stats}))
+                    sys.exit(1)
+                i += 1
+        finally:
+            import shutil
+            shutil.rmtree(base, ignore_errors=True)
+        print(json.dumps({"trials": i, "seed": a.seed, "seconds": round(time.time() - t0, 1), "mismatches": 0, **stats}))
+        return
     ctx = Context(0)
     stats = dict(device=0, host=0, damage=0, pages=0, n_zero=0, n_data=0, n_dup=0, n_parent=0, n_peer=0)
     t0, i = time.time(), 0
