@@ -4,7 +4,6 @@ import numpy as np
 import pytest
 import torch
 
-import oracle_lib as O
 from helpers import PAGE, mixed_image, special_pages
 
 pytestmark = pytest.mark.gpu

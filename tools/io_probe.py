@@ -1,6 +1,5 @@
 """tmpfs <-> pinned-memory file I/O rates with N threads (development aid)."""
 import os
-import sys
 import threading
 import time
 
