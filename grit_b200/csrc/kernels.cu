@@ -59,7 +59,10 @@ __device__ __forceinline__ unsigned long long fmix(unsigned long long x) {
 
 __device__ __forceinline__ uint4 ldg_stream(const uint4* p) {
   uint4 v;
-  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+  // .L2::256B: fetch the 256-byte aligned block around the line into L2 -- the other half is what this lane group
+  // reads one step later (or read one step earlier), and DRAM serves 256 contiguous bytes better than 2 x 128
+  // (k_analyze 2.81 -> 2.755 ms on the 16 GB image; DRAM traffic unchanged, every line is still fetched once)
+  asm volatile("ld.global.nc.L1::no_allocate.L2::256B.v4.u32 {%0,%1,%2,%3}, [%4];"
                : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
                : "l"(p));
   return v;
@@ -305,7 +308,7 @@ constexpr uint32_t kSmRingBase = kSmBytes;       // behind the tables
 constexpr uint32_t kSmBytesWT = kSmBytes + kSmRing * kThreads * 16;  // 225 280 B of the 232 448 B limit
 
 __device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void* gptr) {
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(gptr) : "memory");
+  asm volatile("cp.async.cg.shared.global.L2::256B [%0], [%1], 16;" ::"r"(smem_addr), "l"(gptr) : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
