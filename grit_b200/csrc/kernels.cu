@@ -302,10 +302,12 @@ k_analyze(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ image, u
 // algorithmic minimum, instead of N + 2N.
 // CRC + hash64 + a register load ring + stores do not fit 128 registers, so here the load ring
 // lives in shared memory: each lane's 16-byte loads are cp.async copies (global -> shared, no
-// register) into a private slot that the same lane reads back with one LDS.128 seven steps later.
-constexpr int kSmRing = 7;                       // cp.async copies each lane keeps in flight
+// register) into a private slot that the same lane reads back with one LDS.128 kSmRing steps later.
+// Depth measured on the 16 GB dense image (pack, ms): 2: 7.49, 3: 6.40, 4: 5.94-6.10, 5: 5.79-5.83, 6: 5.93-5.97, 7: 6.10-6.13,
+// 8: slower again.  Five copies per lane (40 KB per SM) cover the read latency; more only crowd the stores out.
+constexpr int kSmRing = 5;                       // cp.async copies each lane keeps in flight
 constexpr uint32_t kSmRingBase = kSmBytes;       // behind the tables
-constexpr uint32_t kSmBytesWT = kSmBytes + kSmRing * kThreads * 16;  // 225 280 B of the 232 448 B limit
+constexpr uint32_t kSmBytesWT = kSmBytes + kSmRing * kThreads * 16;  // 208 896 B of the 232 448 B limit
 
 __device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void* gptr) {
   asm volatile("cp.async.cg.shared.global.L2::256B [%0], [%1], 16;" ::"r"(smem_addr), "l"(gptr) : "memory");
