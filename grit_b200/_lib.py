@@ -72,6 +72,7 @@ SYMBOLS = {
     "grit_dedup_pages": (_I, [_P, _U64, _P, _P, _P, C.POINTER(Table), C.POINTER(Table), _U32, _P] + _ERR),
     "grit_compact_pages": (_I, [_P, _P, _U64, _P, _P, _U64, _U64, C.POINTER(_U64), _P] + _ERR),
     "grit_compact_pages_static": (_I, [_I, _P, _U64, _P, _P, _U64, _U64, C.POINTER(_U64), _P] + _ERR),
+    "grit_compact_pages_static_warmup": (_I, [_I] + _ERR),
     "grit_pack_buffer": (_I, [_P, _P, _U64, C.POINTER(Table), C.POINTER(Table), _U32, _P, _U64, _P, _P, _P,
                               C.POINTER(PackStats), _P] + _ERR),
     "grit_restore_buffer": (_I, [_P, _P, _U64, _P, _P, _U64, _P, _U64, C.POINTER(_P), C.POINTER(_U64), _U32, _P, _I,

@@ -608,7 +608,9 @@ struct ImageCache {
     void* d = nullptr;
     uint64_t pages = 0;
   };
-  std::vector<std::pair<std::string, Img>> items;
+  // a deque: entries keep their address while later ones are added (load_dependencies holds a pointer to the
+  // parent's entry across the loads of the peers)
+  std::deque<std::pair<std::string, Img>> items;
   void release() {
     for (auto& it : items) cudaFree(it.second.d);
     items.clear();

@@ -10,10 +10,20 @@
 // cannot afford the device-wide synchronisation cudaMalloc and cudaFree imply,
 // or are handed a fixed set of buffers by a host runtime that forbids any
 // further allocation.  For them the working memory lives in the array below,
-// inside the library image: it exists on every GPU that loads libgritpack.so,
-// from load until the process exits, and costs kScratchBytes (about 129 KiB)
-// there.  The price is a fixed upper bound on the image size and one shared
-// scratch area per device.
+// inside the library image, and costs kScratchBytes (about 137 KiB) on every
+// GPU that has used it, from that GPU's first use until the process exits.
+// The price is a fixed upper bound on the image size and one shared scratch
+// area per device.
+//
+// "From first use", not "from load": the CUDA runtime loads device code lazily
+// (the default since CUDA 12.2).  The array comes into being on a device when
+// its address is first asked for, and the compaction kernel is loaded at its
+// first launch; both are the driver's own device-memory allocations and they
+// happen inside the first call on that device.  A caller that will run when
+// memory is short therefore calls grit_compact_pages_static_warmup(device)
+// once at start-up, while memory is plentiful: it does the set-up and runs a
+// one-page compaction on buffers that live in the array itself, so that every
+// later call finds array and kernel resident and allocates nothing at all.
 #include <mutex>
 
 #include "ctx.h"
@@ -23,12 +33,14 @@ using namespace grit;
 constexpr uint64_t kMaxPages = GRIT_STATIC_MAX_PAGES;
 constexpr uint64_t kMaxTiles = (kMaxPages + kCompactTile - 1) / kCompactTile;
 constexpr uint64_t kCounterWords = 32;  // 256 bytes reserved for DevCounters, keeps the status words aligned
-constexpr uint64_t kScratchWords = kCounterWords + kMaxTiles;
+// behind the status words: the buffers of the warm-up's one-page compaction (image page, packed page, one reference)
+constexpr uint64_t kWarmWords = (2 * kPage + 256) / sizeof(unsigned long long);
+constexpr uint64_t kScratchWords = kCounterWords + kMaxTiles + kWarmWords;
 constexpr uint64_t kScratchBytes = kScratchWords * sizeof(unsigned long long);
 static_assert(sizeof(DevCounters) <= kCounterWords * sizeof(unsigned long long), "counter block too small");
 static_assert(kScratchBytes <= 160 * 1024, "the scratch every GPU keeps resident must stay modest");
 
-// [0, 32): DevCounters.  [32, 32 + kMaxTiles): tile status words of the look-back scan.
+// [0, 32): DevCounters.  [32, 32 + kMaxTiles): tile status words of the look-back scan.  Then the warm-up buffers.
 static __device__ __align__(256) unsigned long long g_scratch[kScratchWords];
 
 namespace {
@@ -46,7 +58,6 @@ std::mutex g_setup_mu;
 // device's copy of g_scratch lives.  In host code `g_scratch` is only a handle
 // for that query; its own address is a host address and must never reach a kernel.
 int setup_device(int device, PerDevice** out, char* err, size_t errlen) {
-  if (device < 0 || device >= kMaxDevices) return fail(err, errlen, GRIT_EINVAL, "device %d out of range", device);
   std::lock_guard<std::mutex> g(g_setup_mu);
   PerDevice& d = g_dev[device];
   if (!d.ready) {
@@ -65,6 +76,24 @@ int setup_device(int device, PerDevice** out, char* err, size_t errlen) {
   return GRIT_OK;
 }
 
+// Makes `device` current for the call and puts the caller's device back on the way out.
+struct DeviceScope {
+  int prev = -1;
+  int enter(int device, char* err, size_t errlen) {
+    int n = 0;
+    GRIT_CUDA(cudaGetDeviceCount(&n));
+    if (device < 0 || device >= n || device >= kMaxDevices)
+      return fail(err, errlen, GRIT_EINVAL, "device %d out of range (%d device(s))", device, n);
+    GRIT_CUDA(cudaGetDevice(&prev));
+    if (prev != device) GRIT_CUDA(cudaSetDevice(device));
+    else prev = -1;
+    return GRIT_OK;
+  }
+  ~DeviceScope() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
 }  // namespace
 
 extern "C" int grit_compact_pages_static(int device, const void* d_image, uint64_t n_pages, uint32_t* d_ref,
@@ -79,7 +108,8 @@ extern "C" int grit_compact_pages_static(int device, const void* d_image, uint64
   if ((reinterpret_cast<uintptr_t>(d_image) | reinterpret_cast<uintptr_t>(d_packed)) & 15)
     return fail(err, errlen, GRIT_EINVAL, "buffer is not 16-byte aligned");
   if (n_pages && (!d_image || !d_ref || (!d_packed && capacity_pages))) return fail(err, errlen, GRIT_EINVAL, "null buffer");
-  GRIT_CUDA(cudaSetDevice(device));
+  DeviceScope scope;
+  if (int rc = scope.enter(device, err, errlen)) return rc;
   PerDevice* d = nullptr;
   if (int rc = setup_device(device, &d, err, errlen)) return rc;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
@@ -99,5 +129,24 @@ extern "C" int grit_compact_pages_static(int device, const void* d_image, uint64
   if (host.overflow)
     return fail(err, errlen, GRIT_EINVAL, "packed buffer too small: %llu pages did not fit capacity %llu",
                 (unsigned long long)host.overflow, (unsigned long long)capacity_pages);
+  return GRIT_OK;
+}
+
+// Start-up call for grit_compact_pages_static: brings the scratch array and the compaction kernel onto `device`
+// (the driver allocates for both the first time they are used) by compacting one non-zero page that lives in the
+// array itself.  Nothing is allocated by this library here either; what is allocated is the driver's, and only once.
+extern "C" int grit_compact_pages_static_warmup(int device, char* err, size_t errlen) {
+  DeviceScope scope;
+  if (int rc = scope.enter(device, err, errlen)) return rc;
+  PerDevice* d = nullptr;
+  if (int rc = setup_device(device, &d, err, errlen)) return rc;
+  unsigned char* warm = reinterpret_cast<unsigned char*>(d->scratch + kCounterWords + kMaxTiles);
+  uint32_t* ref = reinterpret_cast<uint32_t*>(warm + 2 * kPage);
+  const uint32_t keep = kRefKeep;
+  GRIT_CUDA(cudaMemsetAsync(warm, 0x5A, kPage, nullptr));
+  GRIT_CUDA(cudaMemcpyAsync(ref, &keep, sizeof keep, cudaMemcpyHostToDevice, nullptr));
+  uint64_t stored = 0;
+  if (int rc = grit_compact_pages_static(device, warm, 1, ref, warm + kPage, 1, 0, &stored, nullptr, err, errlen)) return rc;
+  if (stored != 1) return fail(err, errlen, GRIT_ECUDA, "warm-up compaction stored %llu pages, expected 1", (unsigned long long)stored);
   return GRIT_OK;
 }

@@ -167,9 +167,8 @@ int grit_compact_pages(grit_ctx *ctx, const void *d_image, uint64_t n_pages,
 /* K3 for callers that must not allocate.  It has no counterpart in the reference.
  * Same inputs, outputs and results as grit_compact_pages, but no grit_ctx and no
  * cudaMalloc, cudaMallocHost or cudaFree, on any call: the scan's working memory
- * (one status word per 256-page tile plus a counter block, 129 KiB in all) is a
- * fixed array inside the library image, present on every GPU that loads the
- * library until the process exits.  Meant for a packer that runs while the
+ * (one status word per 256-page tile plus a counter block, 137 KiB in all) is a
+ * fixed array inside the library image.  Meant for a packer that runs while the
  * checkpointed job's allocator holds nearly all of HBM (an allocation could
  * fail, or force that allocator to give memory back), for callers that cannot
  * take the device-wide synchronisation cudaMalloc/cudaFree imply, and for host
@@ -178,18 +177,33 @@ int grit_compact_pages(grit_ctx *ctx, const void *d_image, uint64_t n_pages,
  *     GRIT_EINVAL; use grit_compact_pages for larger images.
  *   - The first call on a device looks up the array's device address
  *     (cudaGetSymbolAddress) and reads two device attributes; make that first
- *     call before starting any stream capture.
+ *     call before starting any stream capture.  The CUDA runtime loads device
+ *     code lazily: the array comes into being on a GPU at that first look-up and
+ *     the kernel at its first launch, and the driver allocates device memory
+ *     for both then -- so the first call is also the one that can still run out
+ *     of memory.  Call grit_compact_pages_static_warmup(device) once at
+ *     start-up, while memory is plentiful: it does the look-up and a one-page
+ *     compaction on buffers inside the array, after which no call on that
+ *     device causes any allocation, the driver's included.  From then on the
+ *     GPU holds the array until the process exits.
  *   - All calls on a device share the one array.  Each call clears what it needs
  *     on `stream` before the kernel, so calls issued one after another are
  *     independent; two calls whose GPU work overlaps (different streams or
  *     threads) race on it and give wrong results -- serialise them.
- *   - Synchronises `stream` before returning (to report *n_stored). */
+ *   - Blocks until the work on `stream` is done (it reports *n_stored, read back
+ *     through a small device-to-host copy).  The caller's current device is
+ *     left as it was.  A device ordinal the process does not have is GRIT_EINVAL. */
 #define GRIT_STATIC_MAX_PAGES (1u << 22)
 int grit_compact_pages_static(int device, const void *d_image, uint64_t n_pages,
                               uint32_t *d_ref, void *d_packed,
                               uint64_t capacity_pages, uint64_t slot_base,
                               uint64_t *n_stored, void *stream, char *err,
                               size_t errlen);
+/* Start-up companion of grit_compact_pages_static (no reference counterpart):
+ * makes the scratch array and the compaction kernel resident on `device` by
+ * compacting one page held in the array itself.  Uses the default stream and
+ * blocks until done.  Idempotent; one call per device that will be used. */
+int grit_compact_pages_static_warmup(int device, char *err, size_t errlen);
 
 /* K1+K2+K3 on one device-resident image; the unit bench.py times as `value`.
  * For a full image (no parent, no peers) K1 first samples 4096 pages: if none of

@@ -294,3 +294,48 @@ def test_directory_cross_rank_peers(oracle, tmp_path):
     assert str(pvs[0]) in copy.ImageDependencies(str(pvs[2]), recursive=False)      # named, though gone
     with pytest.raises(_lib.GritError):
         copy.TransferData(str(pvs[2]), str(tmp_path / "nope"), copy.DOWNLOAD)
+
+
+def test_directory_incremental_checkpoint_of_a_multi_rank_job(oracle, tmp_path):
+    """Three ranks, two checkpoints each: the second is packed against the first as parent AND against the lower
+    ranks' second checkpoints as peers, so a restore of rank 2 loads a parent and two peer images (each with a parent
+    of its own) before it can follow its references."""
+    from grit_b200 import copy
+    shared = np.frombuffer(oracle.synth_image(2500, 0xBA5E, pct_zero=0, pct_dup=0).tobytes(), np.uint8)
+    srcs, pv1, pv2 = [], [], []
+    for r in range(3):
+        src = tmp_path / f"host{r}" / "main" / "checkpoint"
+        src.mkdir(parents=True)
+        (src / "pages-1.img").write_bytes(shared.tobytes())
+        (src / "pages-2.img").write_bytes(oracle.synth_image(600 + 40 * r, 200 + r, pct_zero=10, pct_dup=10, dup_pool=4).tobytes())
+        srcs.append(tmp_path / f"host{r}")
+        pv1.append(tmp_path / "pv" / f"c1-rank{r}")
+        pv2.append(tmp_path / "pv" / f"c2-rank{r}")
+    for r in range(3):
+        peers = [copy.read_tables(str(pv1[q])) + (str(pv1[q]),) for q in range(r)]
+        copy.TransferData(str(srcs[r]), str(pv1[r]), copy.UPLOAD, peers=peers)
+    # the job runs on: every rank dirties pages of its private file, all ranks apply the same update to the weights
+    rng = np.random.default_rng(5)
+    new_w = shared.copy()
+    for p in rng.choice(2500, 300, replace=False):
+        new_w[p * PAGE:(p + 1) * PAGE] = rng.integers(0, 256, PAGE, dtype=np.uint8)
+    for r in range(3):
+        (srcs[r] / "main/checkpoint/pages-1.img").write_bytes(new_w.tobytes())
+        with open(srcs[r] / "main/checkpoint/pages-2.img", "r+b") as f:
+            for p in (3 + r, 100, 555):
+                f.seek(p * PAGE)
+                f.write(bytes([r + 1]) * PAGE)
+    stats = []
+    for r in range(3):
+        peers = [copy.read_tables(str(pv2[q])) + (str(pv2[q]),) for q in range(r)]
+        stats.append(copy.TransferData(str(srcs[r]), str(pv2[r]), copy.UPLOAD, parent_dir=str(pv1[r]), peers=peers))
+    assert stats[0]["n_parent"] > 2000 and stats[0]["n_peer"] == 0 and stats[0]["n_data"] >= 300
+    for r in (1, 2):
+        assert stats[r]["n_parent"] > 2000 and stats[r]["n_peer"] >= 300      # the updated weights come from rank 0
+    deps = copy.ImageDependencies(str(pv2[2]))
+    assert set(deps) >= {str(pv1[2]), str(pv2[0]), str(pv2[1])}
+    for r in (2, 1, 0):
+        back = tmp_path / f"back{r}"
+        st = copy.TransferData(str(pv2[r]), str(back), copy.DOWNLOAD)
+        assert st["n_bad"] == 0
+        assert tree_snapshot(str(back)) == tree_snapshot(str(srcs[r]))
