@@ -75,6 +75,14 @@ SYMBOLS = {
     "grit_compact_pages_static_warmup": (_I, [_I] + _ERR),
     "grit_pack_buffer": (_I, [_P, _P, _U64, C.POINTER(Table), C.POINTER(Table), _U32, _P, _U64, _P, _P, _P,
                               C.POINTER(PackStats), _P] + _ERR),
+    "grit_comm_new_id": (_I, [_P] + _ERR),
+    "grit_comm_create": (_I, [_P, _I, _I, _P, C.POINTER(_P)] + _ERR),
+    "grit_comm_destroy": (None, [_P]),
+    "grit_comm_rank": (_I, [_P]),
+    "grit_comm_world": (_I, [_P]),
+    "grit_pack_buffer_ranked": (_I, [_P, _P, _U64, _U64, C.POINTER(Table), _P, _U64, _P, _P, _P, C.POINTER(PackStats),
+                                     _P] + _ERR),
+    "grit_comm_broadcast": (_I, [_P, _P, _U64, _I, _P] + _ERR),
     "grit_restore_buffer": (_I, [_P, _P, _U64, _P, _P, _U64, _P, _U64, C.POINTER(_P), C.POINTER(_U64), _U32, _P, _I,
                                  C.POINTER(RestoreStats), _P] + _ERR),
     "grit_synth_image": (_I, [_P, _P, _U64, _U64, _U64, _U32, _U32, _U32, _P] + _ERR),

@@ -101,6 +101,29 @@ bool staged_pack() {
   return v;
 }
 
+// The staged dedup: this image's hashes enter a table sized by this image alone, the other images' lists (parent,
+// lower ranks) only probe it -- a hit lowers the owner, a miss touches nothing -- then every page reads its owner.
+int dedup_views_async(grit_ctx* ctx, uint64_t n_pages, const uint32_t* d_crc, const uint64_t* d_hash, uint32_t* d_ref,
+                      const PeerCrcs& crcs, const ProbeLists& lists, cudaStream_t s, char* err, size_t errlen,
+                      cudaEvent_t lists_ready) {
+  DedupTable t{};
+  if (int rc = ensure_table(ctx, n_pages, &t, err, errlen)) return rc;
+  GRIT_CUDA(cudaMemsetAsync(t.keys, 0, (t.mask + 1) * sizeof(unsigned long long), s));
+  GRIT_CUDA(cudaMemsetAsync(t.vals, 0xFF, (t.mask + 1) * sizeof(uint32_t), s));
+  GRIT_CUDA(launch_table_insert(ctx->geom, t, d_hash, d_ref, n_pages, kOriginSelf, 0, s));
+  ctx->launches++;
+  bool any = false;
+  for (int o = 0; o < 9; o++) any = any || (lists.n[o] && lists.hash[o]);
+  if (any) {
+    if (lists_ready) GRIT_CUDA(cudaStreamWaitEvent(s, lists_ready, 0));  // the lists may still be arriving
+    GRIT_CUDA(launch_table_probe_lists(ctx->geom, t, lists, s));
+    ctx->launches++;
+  }
+  GRIT_CUDA(launch_resolve(ctx->geom, t, 0, n_pages, d_crc, d_hash, d_ref, crcs, s));
+  ctx->launches++;
+  return GRIT_OK;
+}
+
 }  // namespace grit
 
 namespace {
@@ -127,63 +150,40 @@ int dedup_async(grit_ctx* ctx, uint64_t n_pages, const uint32_t* d_crc, const ui
                 size_t errlen, DedupTable* table_out = nullptr, PeerCrcs* crcs_out = nullptr) {
   if (n_peers > GRIT_MAX_PEERS) return fail(err, errlen, GRIT_EINVAL, "n_peers %u > %u", n_peers, GRIT_MAX_PEERS);
   PeerCrcs crcs{};
+  ProbeLists lists{};
   uint64_t items = n_pages;
   const bool parent_on = parent && parent->n_pages;
   if (parent_on) {
     if (parent->n_pages > GRIT_MAX_PAGES) return fail(err, errlen, GRIT_EINVAL, "parent too large");
-    crcs.parent = parent->crc;
+    crcs.parent.base = parent->crc;
+    lists.hash[0].base = reinterpret_cast<const unsigned long long*>(parent->hash);
+    lists.n[0] = parent->n_pages;
   }
   for (uint32_t r = 0; r < n_peers; r++) {
     if (peers[r].n_pages > GRIT_MAX_PAGES) return fail(err, errlen, GRIT_EINVAL, "peer too large");
-    crcs.peer[r] = peers[r].crc;
+    crcs.peer[r].base = peers[r].crc;
+    lists.hash[1 + r].base = reinterpret_cast<const unsigned long long*>(peers[r].hash);
+    lists.n[1 + r] = peers[r].n_pages;
   }
+  if (!table_out) return dedup_views_async(ctx, n_pages, d_crc, d_hash, d_ref, crcs, lists, s, err, errlen);
   // The fused kernel inserts this image's pages itself, after the others: its table must hold them all.
-  // The staged path inserts this image first and only probes with the others, so the table is sized by
-  // this image alone whatever the number of peers.
-  if (table_out) {
-    if (parent_on) items += parent->n_pages;
-    for (uint32_t r = 0; r < n_peers; r++) items += peers[r].n_pages;
-  }
+  if (parent_on) items += parent->n_pages;
+  for (uint32_t r = 0; r < n_peers; r++) items += peers[r].n_pages;
   DedupTable t{};
   if (int rc = ensure_table(ctx, items, &t, err, errlen)) return rc;
   GRIT_CUDA(cudaMemsetAsync(t.keys, 0, (t.mask + 1) * sizeof(unsigned long long), s));
   GRIT_CUDA(cudaMemsetAsync(t.vals, 0xFF, (t.mask + 1) * sizeof(uint32_t), s));
-  if (table_out) {
-    if (parent_on) {
-      GRIT_CUDA(launch_table_insert(ctx->geom, t, parent->hash, nullptr, parent->n_pages, 0, 0, s));
-      ctx->launches++;
-    }
-    for (uint32_t r = 0; r < n_peers; r++)
-      if (peers[r].n_pages) {
-        GRIT_CUDA(launch_table_insert(ctx->geom, t, peers[r].hash, nullptr, peers[r].n_pages, 1 + r, 0, s));
-        ctx->launches++;
-      }
-    *table_out = t;
-    *crcs_out = crcs;
-    return GRIT_OK;
-  }
-  GRIT_CUDA(launch_table_insert(ctx->geom, t, d_hash, d_ref, n_pages, kOriginSelf, 0, s));
-  ctx->launches++;
-  // the parent's and the lower ranks' hashes probe the table in one launch
-  ProbeLists lists{};
-  bool any = false;
   if (parent_on) {
-    lists.hash[0] = reinterpret_cast<const unsigned long long*>(parent->hash);
-    lists.n[0] = parent->n_pages;
-    any = true;
+    GRIT_CUDA(launch_table_insert(ctx->geom, t, parent->hash, nullptr, parent->n_pages, 0, 0, s));
+    ctx->launches++;
   }
   for (uint32_t r = 0; r < n_peers; r++)
     if (peers[r].n_pages) {
-      lists.hash[1 + r] = reinterpret_cast<const unsigned long long*>(peers[r].hash);
-      lists.n[1 + r] = peers[r].n_pages;
-      any = true;
+      GRIT_CUDA(launch_table_insert(ctx->geom, t, peers[r].hash, nullptr, peers[r].n_pages, 1 + r, 0, s));
+      ctx->launches++;
     }
-  if (any) {
-    GRIT_CUDA(launch_table_probe_lists(ctx->geom, t, lists, s));
-    ctx->launches++;
-  }
-  GRIT_CUDA(launch_resolve(ctx->geom, t, 0, n_pages, d_crc, d_hash, d_ref, crcs, s));
-  ctx->launches++;
+  *table_out = t;
+  *crcs_out = crcs;
   return GRIT_OK;
 }
 
@@ -203,6 +203,9 @@ int analyze_through_async(grit_ctx* ctx, const void* d_image, uint64_t n_pages, 
   return GRIT_OK;
 }
 
+}  // namespace
+
+namespace grit {
 int compact_async(grit_ctx* ctx, const void* d_image, uint64_t n_pages, uint32_t* d_ref, void* d_packed,
                   uint64_t capacity_pages, uint64_t slot_base, cudaStream_t s, char* err, size_t errlen) {
   // pages that the write-through K1 of these very buffers put at their own index stay where they are
@@ -218,8 +221,7 @@ int compact_async(grit_ctx* ctx, const void* d_image, uint64_t n_pages, uint32_t
   ctx->launches++;
   return GRIT_OK;
 }
-
-}  // namespace
+}  // namespace grit
 
 extern "C" {
 

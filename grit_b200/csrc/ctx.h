@@ -38,7 +38,7 @@ struct grit_ctx {
     void* p = nullptr;
     size_t cap = 0;
   };
-  Buf dev[24], pin[20];
+  Buf dev[48], pin[20];
 };
 
 namespace grit {
@@ -66,11 +66,20 @@ int ensure_table(grit_ctx* ctx, uint64_t n_items, DedupTable* t, char* err, size
 int ensure_status(grit_ctx* ctx, uint64_t n_pages, char* err, size_t errlen);
 int reset_counters(grit_ctx* ctx, cudaStream_t s, char* err, size_t errlen);
 int read_counters(grit_ctx* ctx, cudaStream_t s, char* err, size_t errlen);  // syncs s
+// K2 with the other images given as views (contiguous arrays or slices gathered by comm.cu); lists_ready, if set,
+// is waited for on s before the lists are read
+int dedup_views_async(grit_ctx* ctx, uint64_t n_pages, const uint32_t* d_crc, const uint64_t* d_hash, uint32_t* d_ref,
+                      const PeerCrcs& crcs, const ProbeLists& lists, cudaStream_t s, char* err, size_t errlen,
+                      cudaEvent_t lists_ready = nullptr);
+// K3 into d_packed (status words sized and cleared here)
+int compact_async(grit_ctx* ctx, const void* d_image, uint64_t n_pages, uint32_t* d_ref, void* d_packed,
+                  uint64_t capacity_pages, uint64_t slot_base, cudaStream_t s, char* err, size_t errlen);
 // cached device / pinned-host buffer number `id` of at least `bytes` bytes (contents undefined)
 int ctx_dev(grit_ctx* ctx, int id, size_t bytes, void** out, char* err, size_t errlen);
 int ctx_pin(grit_ctx* ctx, int id, size_t bytes, void** out, char* err, size_t errlen);
 enum DevBuf { kDevIn0 = 0, kDevOut0 = 3, kDevRef = 6, kDevCrc, kDevHash, kDevParentHash, kDevParentCrc,
-              kDevRPacked, kDevRRef, kDevRCrc, kDevROut0 = 14, kDevRParent = 17 };
+              kDevRPacked, kDevRRef, kDevRCrc, kDevROut0 = 14, kDevRParent = 17,
+              kDevPeerHash0 = 18 /* ..25 */, kDevPeerCrc0 = 26 /* ..33 */, kDevCommHash = 34, kDevCommCrc, kDevCommPad };
 enum PinBuf { kPinIn0 = 0, kPinOut0 = 3, kPinCounts = 6, kPinMeta0 = 7, kPinRStageOut0 = 10, kPinRStageIn0 = 13 /* ..15 */ };
 bool write_through_pack();  // false with GRITPACK_WRITE_THROUGH=0
 bool staged_pack();  // true unless GRITPACK_FUSED=1 selects the experimental single-pass pack kernel

@@ -54,8 +54,7 @@ PackStream::~PackStream() {
     if (ev_kern_[b]) cudaEventDestroy(ev_kern_[b]);
     if (ev_d2h_[b]) cudaEventDestroy(ev_d2h_[b]);
   }
-  for (void* p : d_peer_bufs_) cudaFree(p);
-  // the other buffers belong to the context's cache and stay for the next call
+  // the buffers belong to the context's cache and stay for the next call
 }
 
 int PackStream::begin(const grit_table* parent, char* err, size_t errlen, const grit_table* peers, uint32_t n_peers) {
@@ -84,7 +83,7 @@ int PackStream::begin(const grit_table* parent, char* err, size_t errlen, const 
     if (int rc = ctx_dev(ctx_, kDevParentCrc, parent->n_pages * 4, (void**)&d_parent_crc_, err, errlen)) return rc;
     GRIT_CUDA(cudaMemcpyAsync(d_parent_hash_, parent->hash, parent->n_pages * 8, cudaMemcpyHostToDevice, ctx_->stream));
     GRIT_CUDA(cudaMemcpyAsync(d_parent_crc_, parent->crc, parent->n_pages * 4, cudaMemcpyHostToDevice, ctx_->stream));
-    crcs_.parent = d_parent_crc_;
+    crcs_.parent.base = d_parent_crc_;
     h2d_bytes += parent->n_pages * 12.0;
   }
   if (n_peers > GRIT_MAX_PEERS) return fail(err, errlen, GRIT_EINVAL, "n_peers %u > %u", n_peers, GRIT_MAX_PEERS);
@@ -104,14 +103,12 @@ int PackStream::begin(const grit_table* parent, char* err, size_t errlen, const 
   }
   for (uint32_t r = 0; r < n_peers; r++) {
     if (!peers[r].n_pages) continue;
-    void *dh = nullptr, *dc = nullptr;
-    GRIT_CUDA(cudaMalloc(&dh, peers[r].n_pages * 8));
-    d_peer_bufs_.push_back(dh);
-    GRIT_CUDA(cudaMalloc(&dc, peers[r].n_pages * 4));
-    d_peer_bufs_.push_back(dc);
+    void *dh = nullptr, *dc = nullptr;  // cached in the context like every other working buffer
+    if (int rc = ctx_dev(ctx_, kDevPeerHash0 + (int)r, peers[r].n_pages * 8, &dh, err, errlen)) return rc;
+    if (int rc = ctx_dev(ctx_, kDevPeerCrc0 + (int)r, peers[r].n_pages * 4, &dc, err, errlen)) return rc;
     GRIT_CUDA(cudaMemcpyAsync(dh, peers[r].hash, peers[r].n_pages * 8, cudaMemcpyHostToDevice, s));
     GRIT_CUDA(cudaMemcpyAsync(dc, peers[r].crc, peers[r].n_pages * 4, cudaMemcpyHostToDevice, s));
-    crcs_.peer[r] = static_cast<const uint32_t*>(dc);
+    crcs_.peer[r].base = static_cast<const uint32_t*>(dc);
     h2d_bytes += peers[r].n_pages * 12.0;
     GRIT_CUDA(launch_table_insert(ctx_->geom, table_, static_cast<const uint64_t*>(dh), nullptr, peers[r].n_pages, 1 + r, 0, s));
     ctx_->launches++;

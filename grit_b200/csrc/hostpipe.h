@@ -72,7 +72,6 @@ class PackStream {
   uint64_t* d_hash_ = nullptr;
   uint64_t* d_parent_hash_ = nullptr;
   uint32_t* d_parent_crc_ = nullptr;
-  std::vector<void*> d_peer_bufs_;  // peers' tables on the device (owned)
   uint64_t chunk_page0_[kPipeDepth] = {};
   DedupTable table_{};
   PeerCrcs crcs_{};

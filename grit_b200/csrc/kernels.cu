@@ -442,11 +442,12 @@ k_table_insert(DedupTable t, const unsigned long long* __restrict__ hash, const 
 __global__ void __launch_bounds__(256)
 k_table_probe_lists(DedupTable t, ProbeLists lists) {
   const uint32_t origin = blockIdx.y;
-  const unsigned long long* __restrict__ hash = lists.hash[origin];
+  const ListView<unsigned long long> hash = lists.hash[origin];
   const uint64_t n = lists.n[origin];
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
        i += (uint64_t)gridDim.x * blockDim.x) {
     const unsigned long long h = hash[i];
+    if (h == 0ull) continue;  // hash64 is never 0: padding of a gathered slice, or a damaged hashes.bin
     for (uint64_t s = table_home(h, t.mask);; s = (s + 1) & t.mask) {
       const unsigned long long k = t.keys[s];
       if (k == h) {
@@ -1070,7 +1071,8 @@ cudaError_t launch_table_insert(const LaunchGeom& g, DedupTable t, const uint64_
 
 cudaError_t launch_table_probe_lists(const LaunchGeom& g, DedupTable t, const ProbeLists& lists, cudaStream_t s) {
   uint64_t longest = 0;
-  for (int o = 0; o < 9; o++) longest = std::max(longest, lists.n[o]);
+  for (int o = 0; o < 9; o++)
+    if (lists.hash[o]) longest = std::max(longest, lists.n[o]);
   if (!longest) return cudaSuccess;
   dim3 grid(grid_for(g, longest, 256, 8), 9);  // an origin without a list costs a few empty blocks
   k_table_probe_lists<<<grid, 256, 0, s>>>(t, lists);

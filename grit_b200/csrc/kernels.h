@@ -22,14 +22,28 @@ struct DedupTable {
   uint64_t mask;  // capacity - 1, capacity a power of two
 };
 
+// A per-page array of another image.  Plain arrays are contiguous; arrays that arrived through the cross-rank
+// exchange (comm.cu) come in slices of 2^shift pages, every rank's slice s side by side: element i lives at
+// base[(i >> shift) * stride + (i & (2^shift - 1))].  shift = 26 (GRIT_MAX_PAGES) makes that base[i].
+template <class T>
+struct ListView {
+  const T* base = nullptr;
+  uint64_t stride = 0;
+  uint32_t shift = 26;
+  __host__ __device__ const T& operator[](uint64_t i) const {
+    return base[(i >> shift) * stride + (i & ((1ull << shift) - 1))];
+  }
+  __host__ __device__ explicit operator bool() const { return base != nullptr; }
+};
+
 struct PeerCrcs {
-  const uint32_t* parent;
-  const uint32_t* peer[8];
+  ListView<uint32_t> parent;
+  ListView<uint32_t> peer[8];
 };
 
 // the hash lists of the images a pack may refer to, probed against this image's table in one launch
 struct ProbeLists {
-  const unsigned long long* hash[9];  // [0] parent, [1 + r] rank r
+  ListView<unsigned long long> hash[9];  // [0] parent, [1 + r] rank r
   uint64_t n[9];
 };
 

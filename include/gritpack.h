@@ -219,6 +219,51 @@ int grit_pack_buffer(grit_ctx *ctx, const void *d_image, uint64_t n_pages,
                      grit_pack_stats *stats, void *stream, char *err,
                      size_t errlen);
 
+/* ---- cross-rank dedup of a multi-GPU job ----------------------------------
+ * One process per GPU, each packs its own rank's image; the ranks exchange only
+ * their per-page (hash64, CRC-32C) tables, 12 bytes per 4 KiB page, with NCCL
+ * over NVLink inside the library.  The reference has no
+ * counterpart: it runs one agent Job per pod and has no cross-pod step
+ * (docs/proposals/20250221-gpu-workload-checkpointing-and-restoration.md:63-65).
+ * NCCL (libnccl.so.2) is loaded at the first of these calls; a process that
+ * never makes one does not need it.  A job has at most GRIT_MAX_PEERS ranks. */
+#define GRIT_COMM_ID_BYTES 128 /* sizeof(ncclUniqueId) */
+typedef struct grit_comm grit_comm;
+
+/* Rank 0 makes the rendezvous id (ncclGetUniqueId) and hands its 128 bytes to the
+ * other ranks by any channel it has (a file on the shared PV, a Job annotation,
+ * an environment variable, MPI, torch.distributed). */
+int grit_comm_new_id(void *id, char *err, size_t errlen);
+/* Collective over all ranks: joins rank `rank` of `world` on the context's GPU. */
+int grit_comm_create(grit_ctx *ctx, int rank, int world, const void *id,
+                     grit_comm **out, char *err, size_t errlen);
+void grit_comm_destroy(grit_comm *comm);
+int grit_comm_rank(const grit_comm *comm);
+int grit_comm_world(const grit_comm *comm);
+
+/* grit_pack_buffer for one rank of a job (collective: every rank calls it, each
+ * with its own image).  K1 runs in slices; each slice's hashes are all-gathered
+ * on a second stream while K1 works on the next one, straight into the device
+ * buffers K2 probes; pages a lower rank already holds become PEER references
+ * (lowest rank owns a page, the parent before any rank).  Ranks may hold
+ * different page counts: max_pages is the largest of them if the caller knows
+ * it (the same value on every rank), or 0 to have the ranks agree on it first,
+ * which costs one small exchange and a host synchronisation.
+ * stats->stage_ms: K1 | exchange wait + K2 | K3. */
+int grit_pack_buffer_ranked(grit_comm *comm, const void *d_image,
+                            uint64_t n_pages, uint64_t max_pages,
+                            const grit_table *parent, void *d_packed,
+                            uint64_t capacity_pages, uint32_t *d_ref,
+                            uint32_t *d_crc, uint64_t *d_hash,
+                            grit_pack_stats *stats, void *stream, char *err,
+                            size_t errlen);
+/* ncclBroadcast of a device buffer from rank `root`, asynchronous on `stream`:
+ * how the ranks hand each other restored images (or any other bytes) without a
+ * second communication library, e.g. the lower ranks' images that
+ * grit_restore_buffer needs in order to follow PEER references. */
+int grit_comm_broadcast(grit_comm *comm, void *d_buf, uint64_t bytes, int root,
+                        void *stream, char *err, size_t errlen);
+
 /* K4: inverse scatter.  Every page of d_out is written: zeros, the packed slot,
  * the owner's slot, or the page of the parent / peer image (device pointers,
  * fully restored).  With verify != 0 the CRC-32C of every non-zero page is
