@@ -222,10 +222,23 @@ int grit_pack_buffer_ranked(grit_comm* c, const void* d_image, uint64_t n_pages,
   }
   LaunchGeom k1_geom = ctx->geom;  // leave NCCL its SMs while slices are still in flight
   if (W > 1) k1_geom.sm_count = std::max(1, ctx->geom.sm_count - comm_ctas());
+  // Rank 0 refers to no other rank: without a parent its image may be dense (weights, optimizer state) and K1 can
+  // store the pages to their own slots as in grit_pack_buffer.  The ranks above mostly hold pages rank 0 owns.
+  const bool try_through = c->rank == 0 && !(parent && parent->n_pages) && n_pages && d_packed && write_through_pack();
+  if (try_through) {
+    GRIT_CUDA(cudaMemsetAsync(&ctx->d_cnt->first_drop, 0xFF, sizeof(unsigned long long), s));
+    GRIT_CUDA(launch_probe_dense(d_image, n_pages, ctx->d_cnt, s));
+    ctx->launches++;
+  }
 
   for (uint64_t i = 0; i < std::max<uint64_t>(n_slices, 1); i++) {
     const uint64_t p0 = i << shift, have = p0 < n_pages ? std::min(L, n_pages - p0) : 0;
-    if (have) {
+    if (have && try_through) {
+      GRIT_CUDA(launch_analyze_auto(k1_geom, ctx->d_tables, static_cast<const char*>(d_image) + p0 * kPage, have, d_crc + p0,
+                                    d_hash + p0, d_ref + p0, static_cast<char*>(d_packed) + p0 * kPage, capacity_pages, p0,
+                                    ctx->d_cnt, s));
+      ctx->launches += 2;
+    } else if (have) {
       GRIT_CUDA(launch_analyze(k1_geom, ctx->d_tables, static_cast<const char*>(d_image) + p0 * kPage, have, d_crc + p0,
                                d_hash + p0, d_ref + p0, s));
       ctx->launches++;
@@ -253,6 +266,11 @@ int grit_pack_buffer_ranked(grit_comm* c, const void* d_image, uint64_t n_pages,
   }
   if (W > 1 && n_slices) GRIT_CUDA(cudaEventRecord(c->ev_done, cs));
   c->exchanges++;
+  if (try_through) {  // K3 on these buffers leaves in place what K1 stored
+    ctx->through_image = d_image;
+    ctx->through_packed = d_packed;
+    ctx->through_pages = n_pages;
+  }
   GRIT_CUDA(cudaEventRecord(ctx->evA, s));
 
   // K2: the parent and the ranks below this one may own a page (lowest origin wins)
@@ -296,7 +314,7 @@ int grit_pack_buffer_ranked(grit_comm* c, const void* d_image, uint64_t n_pages,
     stats->stage_ms[1] = ms;
     cudaEventElapsedTime(&ms, ctx->evB, ctx->ev1);
     stats->stage_ms[2] = ms;
-    stats->wrote_through = 0;
+    stats->wrote_through = try_through && k.dense_hint;
   }
   if (k.overflow)
     return fail(err, errlen, GRIT_EINVAL, "packed buffer too small: %llu pages did not fit capacity %llu",

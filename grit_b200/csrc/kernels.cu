@@ -326,7 +326,10 @@ __device__ __forceinline__ uint4 lds128(uint32_t smem_addr) {
 __global__ void __launch_bounds__(kThreads, 1)
 k_analyze_through(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ image, uint64_t n_pages,
                   uint32_t* __restrict__ crc, unsigned long long* __restrict__ hash, uint32_t* __restrict__ ref,
-                  uint4* __restrict__ packed, uint64_t capacity_pages, DevCounters* __restrict__ cnt, int want_hint) {
+                  uint4* __restrict__ packed, uint64_t capacity_pages, uint64_t page_base, DevCounters* __restrict__ cnt,
+                  int want_hint) {
+  // image, crc, hash, ref and packed all start at page `page_base` of the whole image (a slice of a ranked pack);
+  // first_drop and capacity_pages count pages of the whole image
   if (want_hint >= 0 && (int)cnt->dense_hint != want_hint) return;  // the other K1 variant runs instead
   load_tables(tabs);
   const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -354,7 +357,7 @@ k_analyze_through(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ 
     a.h = 0;
     const bool on = p < n_pages;
     const unsigned long long first_drop = __ldcg(&cnt->first_drop);
-    const bool through = on && p < capacity_pages && p < first_drop;
+    const bool through = on && page_base + p < capacity_pages && page_base + p < first_drop;
     uint4* d = packed + p * 256 + l;
     const uint64_t p_next = 4 * (grp + stride) + g;
     const uint64_t p_load = grp + stride < n_groups ? (p_next < last ? p_next : last) : (p < last ? p : last);
@@ -381,7 +384,7 @@ k_analyze_through(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ 
       crc[p] = page_crc;
       hash[p] = page_hash;
       ref[p] = z ? kRefPending : 0u;
-      if (!z && p < first_drop) atomicMin(&cnt->first_drop, (unsigned long long)p);
+      if (!z && page_base + p < first_drop) atomicMin(&cnt->first_drop, (unsigned long long)(page_base + p));
     }
     p = p_next;
     src = src_next;
@@ -389,27 +392,59 @@ k_analyze_through(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ 
   cp_async_wait<0>();
 }
 
-// Looks at 4096 evenly spread pages (128 bytes of each): any that reads as zero means the image is not
-// dense and plain K1 + K3 is the cheaper pack.  Sets cnt->dense_hint for the two K1 variants and K3.
-__global__ void __launch_bounds__(256)
+// Decides, from 4096 evenly spread pages (128 bytes of each), whether K1 should write the pages through to their own
+// slots.  That pays when a long prefix of the image stays in place: no duplicate anywhere near the front (a page that
+// is dropped shifts every later slot, and K3 then moves what K1' already wrote) and no zero page in the first quarter
+// (K1' stops storing at the first zero page it meets; the rest is K3's).  So: the lowest sampled zero page must lie
+// beyond a quarter of the image, and fewer than four samples may repeat another sample's 128 bytes.  One block; sets
+// cnt->dense_hint for the two K1 variants and K3.
+constexpr uint32_t kProbeSamples = 4096, kProbeSlots = 8192;
+__global__ void __launch_bounds__(1024)
 k_probe_dense(const uint4* __restrict__ image, uint64_t n_pages, DevCounters* __restrict__ cnt) {
-  __shared__ int s_zero;
-  if (threadIdx.x == 0) s_zero = 0;
-  __syncthreads();
-  const uint32_t n_samples = 4096;
-  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_samples; i += gridDim.x * blockDim.x) {
-    const uint64_t p = (uint64_t)i * n_pages / n_samples;
-    const uint4* q = image + p * 256;
-    uint32_t o = 0;
-#pragma unroll
-    for (int k = 0; k < 8; k++) {
-      const uint4 v = __ldg(q + 32 * k + (i & 31));
-      o |= v.x | v.y | v.z | v.w;
-    }
-    if (o == 0) s_zero = 1;
+  __shared__ uint32_t s_sig[kProbeSlots];
+  __shared__ unsigned long long s_first_zero;
+  __shared__ uint32_t s_repeats;
+  for (uint32_t i = threadIdx.x; i < kProbeSlots; i += blockDim.x) s_sig[i] = 0;
+  if (threadIdx.x == 0) {
+    s_first_zero = ~0ull;
+    s_repeats = 0;
   }
   __syncthreads();
-  if (threadIdx.x == 0 && s_zero) atomicExch(&cnt->dense_hint, 0u);
+  for (uint32_t i = threadIdx.x; i < kProbeSamples; i += blockDim.x) {
+    const uint64_t p = (uint64_t)i * n_pages / kProbeSamples;
+    if (i && p == (uint64_t)(i - 1) * n_pages / kProbeSamples) continue;  // fewer pages than samples
+    const uint4* q = image + p * 256 + (i & 31);  // eight 16-byte pieces, 512 bytes apart; the offset varies by sample
+    uint32_t o = 0;
+    unsigned long long sig = kGold;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      const uint4 v = __ldg(q + 32 * k);
+      o |= v.x | v.y | v.z | v.w;
+      sig = (sig ^ ((unsigned long long)v.y << 32 | v.x)) * kFmul;
+      sig = (sig ^ ((unsigned long long)v.w << 32 | v.z)) * kFmul;
+    }
+    if (o == 0) {  // reads as a zero page
+      atomicMin(&s_first_zero, (unsigned long long)p);
+      continue;
+    }
+    // the sampled bytes differ with the offset, so two samples only compare equal when they read the same offset of
+    // equal pages: signature plus offset
+    uint32_t g = (uint32_t)(sig >> 32) ^ ((i & 31) * 0x9E3779B9u);
+    g = g ? g : 1u;
+    for (uint32_t sl = g & (kProbeSlots - 1);; sl = (sl + 1) & (kProbeSlots - 1)) {
+      const uint32_t was = atomicCAS(&s_sig[sl], 0u, g);
+      if (was == 0u) break;
+      if (was == g) {
+        atomicAdd(&s_repeats, 1u);
+        break;
+      }
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const bool dense = s_first_zero >= n_pages / 4 && s_repeats < 4;
+    cnt->dense_hint = dense ? 1u : 0u;
+  }
 }
 
 // ------------------------------------------------------------------ K2 dedup
@@ -1043,18 +1078,23 @@ cudaError_t launch_analyze(const LaunchGeom& g, const Gf2Tables* d_tab, const vo
   return cudaGetLastError();
 }
 
-// K1 for a full, single-rank image: samples the image, then runs the write-through variant if it looks
-// dense (no zero page among the samples) and plain K1 otherwise -- decided on the device, no host sync.
-// d_cnt->dense_hint must be 1 on entry (reset_counters does that); K3 reads it to skip pages in place.
+// K1 for a full image: runs the write-through variant if the sample (launch_probe_dense) found the image dense and
+// plain K1 otherwise -- decided on the device, no host sync.  K3 reads the same hint to skip pages in place.
+// The arrays may start at page `page_base` of the whole image (sliced K1 of a ranked pack).
+cudaError_t launch_probe_dense(const void* d_image, uint64_t n_pages, DevCounters* d_cnt, cudaStream_t s) {
+  if (!n_pages) return cudaSuccess;
+  k_probe_dense<<<1, 1024, 0, s>>>(static_cast<const uint4*>(d_image), n_pages, d_cnt);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_analyze_auto(const LaunchGeom& g, const Gf2Tables* d_tab, const void* d_image, uint64_t n_pages,
                                 uint32_t* d_crc, uint64_t* d_hash, uint32_t* d_ref, void* d_packed,
-                                uint64_t capacity_pages, DevCounters* d_cnt, cudaStream_t s) {
+                                uint64_t capacity_pages, uint64_t page_base, DevCounters* d_cnt, cudaStream_t s) {
   if (!n_pages) return cudaSuccess;
   const int grid = grid_for(g, (n_pages + 3) / 4, kWarps, 1);
-  k_probe_dense<<<16, 256, 0, s>>>(static_cast<const uint4*>(d_image), n_pages, d_cnt);
   k_analyze_through<<<grid, kThreads, kSmBytesWT, s>>>(d_tab, static_cast<const uint4*>(d_image), n_pages, d_crc,
                                                        reinterpret_cast<unsigned long long*>(d_hash), d_ref,
-                                                       static_cast<uint4*>(d_packed), capacity_pages, d_cnt, 1);
+                                                       static_cast<uint4*>(d_packed), capacity_pages, page_base, d_cnt, 1);
   k_analyze<<<grid, kThreads, kSmBytes, s>>>(d_tab, static_cast<const uint4*>(d_image), n_pages, d_crc,
                                              reinterpret_cast<unsigned long long*>(d_hash), d_ref, d_cnt, 0);
   return cudaGetLastError();

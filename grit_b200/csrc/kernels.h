@@ -92,10 +92,13 @@ cudaError_t launch_compact(const LaunchGeom& g, const void* d_image, uint64_t n_
                            void* d_packed, uint64_t capacity_pages, uint64_t slot_base, bool chained,
                            unsigned long long* d_tile_status, DevCounters* d_cnt, cudaStream_t s,
                            bool in_place = false);
-// K1 for a full single-rank image: write-through variant when the image looks dense, plain K1 otherwise
+// sample of the image -> d_cnt->dense_hint: is writing the pages through to their own slots worth it
+cudaError_t launch_probe_dense(const void* d_image, uint64_t n_pages, DevCounters* d_cnt, cudaStream_t s);
+// K1 for a full image: write-through variant when the hint says dense, plain K1 otherwise.  d_image, the per-page
+// arrays and d_packed start at page `page_base` of the image; capacity_pages counts from the image's first page.
 cudaError_t launch_analyze_auto(const LaunchGeom& g, const Gf2Tables* d_tab, const void* d_image, uint64_t n_pages,
                                 uint32_t* d_crc, uint64_t* d_hash, uint32_t* d_ref, void* d_packed,
-                                uint64_t capacity_pages, DevCounters* d_cnt, cudaStream_t s);
+                                uint64_t capacity_pages, uint64_t page_base, DevCounters* d_cnt, cudaStream_t s);
 // K1+K2+K3 in one pass; crc/hash/ref are the whole image's arrays, the chunk starts at page0 of them
 cudaError_t launch_pack_fused(const LaunchGeom& g, const Gf2Tables* d_tab, const void* d_image, uint64_t n_pages,
                               uint64_t page0, uint32_t* d_crc, uint64_t* d_hash, uint32_t* d_ref, DedupTable t,

@@ -325,6 +325,9 @@ def test_directory_incremental_checkpoint_of_a_multi_rank_job(oracle, tmp_path):
             for p in (3 + r, 100, 555):
                 f.seek(p * PAGE)
                 f.write(bytes([r + 1]) * PAGE)
+            if r:                                   # something only ranks 1 and 2 hold: rank 2 refers to rank 1 for it
+                f.seek(200 * PAGE)
+                f.write(np.frombuffer(oracle.synth_image(20, 0x77, pct_zero=0, pct_dup=0).tobytes(), np.uint8).tobytes())
     stats = []
     for r in range(3):
         peers = [copy.read_tables(str(pv2[q])) + (str(pv2[q]),) for q in range(r)]

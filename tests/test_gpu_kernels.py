@@ -262,17 +262,22 @@ def test_dedup_rule_on_crafted_tables(ctx):
 
 
 def test_dense_images_are_written_through_and_mixed_ones_are_not(ctx, oracle):
-    """grit_pack_buffer samples a full image: dense ones (no zero page) are stored to their own slots by K1 and left in
-    place by K3, the others go through plain K1 + K3; a zero page met after the sample said "dense" ends the
-    write-through.  The bytes are the oracle's in every case."""
+    """grit_pack_buffer samples a full image: where a long prefix would stay in place (no repeated page among the
+    samples, no zero page in the first quarter) K1 stores the pages to their own slots and K3 leaves them there; the
+    others go through plain K1 + K3; a zero page met after the sample said "dense" ends the write-through.  The bytes
+    are the oracle's in every case."""
     n = 6000
     dense = oracle.synth_image(n, 31, pct_zero=0, pct_dup=0)
     late_zero = dense.copy()
     late_zero[5001 * PAGE:5002 * PAGE] = 0            # not among the 4096 sampled pages? either way the result must hold
     dups_only = oracle.synth_image(n, 32, pct_zero=0, pct_dup=30, dup_pool=7)
     mixed = oracle.synth_image(n, 33)
-    for name, img, want_through in (("dense", dense, 1), ("late_zero", late_zero, None), ("dups_only", dups_only, 1),
-                                    ("mixed", mixed, 0)):
+    zero_tail = dense.copy()                           # allocator slack behind the weights: the prefix stays in place
+    zero_tail[5400 * PAGE:5700 * PAGE] = 0
+    early_zero = dense.copy()
+    early_zero[300 * PAGE:340 * PAGE] = 0
+    for name, img, want_through in (("dense", dense, 1), ("late_zero", late_zero, None), ("dups_only", dups_only, 0),
+                                    ("mixed", mixed, 0), ("zero_tail", zero_tail, 1), ("early_zero", early_zero, 0)):
         r = ctx.pack(dev(img))
         o = oracle.pack(img)
         assert np.array_equal(u32(r["ref"]), o["ref"]), name
