@@ -1,20 +1,25 @@
 #!/usr/bin/env python
 """bench.py -- checkpoint pack/restore throughput of gritpack on B200.
 
-Workload (BASELINE.json configs[1]): the device state of a single-GPU PyTorch process holding
-Llama-3-8B random-init bf16 weights: 8 030 261 248 bf16 = 16 060 522 496 B = 3 921 026 pages of
-4 KiB, N(0, 0.02), seed 1234 (+rank).  A step packs that image (CRC-32C + zero detect + hash64 +
-dedup + compaction) and restores it (scatter + CRC verify).  Every step is checked bit-exact
-(restored image == source image) outside the timed region.
+N = 1 (BASELINE.json configs[1]): the device state of a single-GPU PyTorch process holding Llama-3-8B random-init
+bf16 weights: 8 030 261 248 bf16 = 16 060 522 496 B = 3 921 026 pages of 4 KiB, N(0, 0.02), seed 1234.
+N > 1 (configs[2]): one rank of a Phi-3-mini LoRA fine-tune per GPU -- 7.64 GB of base weights with the SAME seed on
+every rank, rank-seeded LoRA/Adam state and workspace, 1 GiB of zeroed allocator slack, 512 MiB of host-side pages
+with the C1 class mix.  The ranks exchange their page tables through grit_comm (NCCL inside libgritpack.so) and the
+ranks above 0 keep PEER references for the weights rank 0 stores.
+A step packs the image (CRC-32C + zero detect + hash64 + dedup + compaction) and restores it (scatter + CRC
+verify).  Every step is checked bit-exact (restored image == source image) outside the timed region.
 
-  value  = image GB moved per second over pack + restore, image and packed image resident in HBM
-           (2 * image bytes / (t_pack + t_restore), whole job over all ranks)
-  e2e    = the same through grit_pack_host / grit_restore_host with PINNED HOST buffers:
-           H2D and D2H copies of every byte are inside the timed region
+  value    = image GB moved per second over pack + restore, image and packed image resident in HBM
+             (2 * image bytes / (t_pack + t_restore), whole job over all ranks)
+  e2e      = the same through grit_pack_host / grit_restore_host with PINNED HOST buffers: H2D and D2H copies of
+             every byte are inside the timed region
+  e2e_dir  = (N = 1) the reference's real boundary: grit_pack_dir + grit_restore_dir + sentinel on directory trees
+             in tmpfs, warm and cold (fresh grit-agent process), beside copy.go restated on the same trees
   roofline = the dominant kernel's algorithmic bytes / its CUDA-event time / measured HBM peak
 
-`--impl reference` times the reference's own data path -- pkg/gritagent/copy/copy.go, through its
-C++ restatement in oracle/ because no Go toolchain exists in this image -- on the host cores.
+`--impl reference` times the reference's own data path -- pkg/gritagent/copy/copy.go, through its C++ restatement
+in oracle/ because no Go toolchain exists in this image -- on the host cores.
 """
 import argparse
 import json
@@ -30,9 +35,33 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 PAGE = 4096
+GiB = 1 << 30
 LLAMA3_8B_PARAMS = 8_030_261_248
+PHI3_MINI_PARAMS = 3_821_079_552
 METRIC = "checkpoint pack/restore GB/s per GPU and 8-GPU aggregate vs roofline; bit-exact"
-WORKLOAD = "llama3-8b-bf16-device-state-16GB pack+restore (BASELINE configs[1])"
+WORKLOAD_1 = "llama3-8b-bf16-device-state-16GB pack+restore (BASELINE configs[1])"
+WORKLOAD_N = "phi3-mini-lora-finetune, one rank per GPU, full checkpoint pack+restore with cross-rank dedup (BASELINE configs[2])"
+
+# configs[2] image of one rank, in pages
+C3_BASE = (PHI3_MINI_PARAMS * 2 + PAGE - 1) // PAGE      # base weights, bf16, same seed on every rank
+C3_LORA = (150 * 10**6) // PAGE                          # LoRA A/B fp32 + Adam m, v: rank-seeded
+C3_WORK = (2 * GiB) // PAGE                              # activations / workspace: rank-seeded random bytes
+C3_SLACK = GiB // PAGE                                   # allocator slack: zeros
+C3_HOST = (512 << 20) // PAGE                            # host-side process pages: C1 class mix
+C3_PAGES = C3_BASE + C3_LORA + C3_WORK + C3_SLACK + C3_HOST
+
+
+def pages_for(world, override=0):
+    if override:
+        return override
+    return (LLAMA3_8B_PARAMS * 2 + PAGE - 1) // PAGE if world == 1 else C3_PAGES
+
+
+def bench_config(world, n_pages):
+    """The `config` object: the same for both arms, a function of the command line only."""
+    return {"workload": WORKLOAD_1 if world == 1 else WORKLOAD_N, "image_bytes_per_gpu": n_pages * PAGE,
+            "pages_per_gpu": n_pages, "seed": 1234,
+            "l2": "inputs (>= 11 GB per step) are larger than the 126 MB L2; no flush needed"}
 
 
 def measured_peak():
@@ -114,25 +143,46 @@ def tmp_root():
     return "/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else tempfile.gettempdir()
 
 
-def write_sample_tree(root, sample_bytes, seed=1234):
-    """A CRIU-style image dir for the sample: the process's memory is one pages-1.img (CRIU writes one per
-    process), plus the small metadata files the copy also has to move."""
+def room_for(n_bytes, copies):
+    """Can `copies` trees of n_bytes live in tmp_root() at once (tmpfs: that is RAM)?"""
+    try:
+        import psutil
+        free_fs = shutil.disk_usage(tmp_root()).free
+        return min(free_fs, psutil.virtual_memory().available) > copies * n_bytes + 8 * GiB
+    except Exception:
+        return False
+
+
+def write_big_file(path, n_bytes, seed=1234):
+    """bf16 N(0, 0.02)-looking bytes; the content is irrelevant to a byte copy, it only must not be sparse."""
     import numpy as np
-    ck = os.path.join(root, "main", "checkpoint")
-    os.makedirs(ck)
     rng = np.random.default_rng(seed)
     blk = (rng.standard_normal(32 << 20, dtype=np.float32) * 0.02).astype(np.float16).tobytes()  # 64 MiB
-    with open(os.path.join(ck, "pages-1.img"), "wb") as f:   # content is irrelevant to a byte copy
-        left = sample_bytes
+    with open(path, "wb") as f:
+        left = n_bytes
         while left > 0:
             n = min(len(blk), left)
             f.write(blk[:n])
             left -= n
+
+
+def write_sample_tree(root, sample_bytes, seed=1234):
+    """A CRIU-style image dir: the process's memory is one pages-1.img (CRIU writes one per process),
+    plus the small metadata files the copy also has to move."""
+    import numpy as np
+    ck = os.path.join(root, "main", "checkpoint")
+    os.makedirs(ck)
+    rng = np.random.default_rng(seed)
+    write_big_file(os.path.join(ck, "pages-1.img"), sample_bytes, seed)
     for name, size in (("inventory.img", 97), ("pagemap-1.img", 1 << 20), ("core-1.img", 4097), ("mm-1.img", 8000)):
         with open(os.path.join(ck, name), "wb") as f:
             f.write(rng.integers(0, 256, size, dtype=np.uint8).tobytes())
     with open(os.path.join(root, "main", "container.log"), "wb") as f:
         f.write(b"stdout F step\n" * 1000)
+
+
+def tree_bytes(root):
+    return sum(os.path.getsize(os.path.join(d, f)) for d, _, fs in os.walk(root) for f in fs)
 
 
 def time_reference_copy(sample_bytes, steps, warmup):
@@ -143,7 +193,7 @@ def time_reference_copy(sample_bytes, steps, warmup):
     try:
         src = os.path.join(base, "host")
         write_sample_tree(src, sample_bytes)
-        logical = sum(os.path.getsize(os.path.join(d, f)) for d, _, fs in os.walk(src) for f in fs)
+        logical = tree_bytes(src)
         times = []
         for i in range(warmup + steps):
             pv, back = os.path.join(base, "pv"), os.path.join(base, "restored")
@@ -167,6 +217,7 @@ def time_reference_copy(sample_bytes, steps, warmup):
 def time_same_work_cpu(sample_pages, threads):
     """The GPU path's work (CRC-32C, hash64, zero detect, dedup, compaction; inverse + verify) on all host threads."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import ctypes as C
     import numpy as np
     import oracle_lib as O
     rng = np.random.default_rng(1234)
@@ -175,7 +226,6 @@ def time_same_work_cpu(sample_pages, threads):
     r = O.pack(img, threads=threads)
     t1 = time.perf_counter()
     out = np.empty_like(img)
-    import ctypes as C
     bad = O.lib().orc_restore_mt(r["packed"].ctypes.data_as(C.c_void_p), r["packed"].size // PAGE,
                                  r["ref"].ctypes.data_as(C.c_void_p), r["crc"].ctypes.data_as(C.c_void_p),
                                  sample_pages, threads, out.ctypes.data_as(C.c_void_p), 1)
@@ -185,23 +235,30 @@ def time_same_work_cpu(sample_pages, threads):
 
 
 def run_reference(args):
+    """Rank 0 alone copies; the other ranks leave at once.  The copy is the image of ONE rank as one pages-1.img (the
+    reference runs one agent Job per pod, copy.go:39-51 gives a file to one worker): the whole image when three
+    copies of it fit in tmpfs and the run stays within minutes, otherwise a 2 GiB sample of it -- the line says which."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
+    world = int(os.environ.get("WORLD_SIZE", str(args.gpus)))
     cores = os.cpu_count() or 1
-    sample = 2 << 30
-    warm = max(1, min(args.warmup, 3))          # a copy has nothing to warm but the page cache: at most three
-    gbs, t, logical = time_reference_copy(sample, max(1, args.steps), warm)
+    n_pages = pages_for(world, args.pages)
+    image_bytes = n_pages * PAGE
+    steps, warm = max(1, args.steps), max(0, args.warmup)
+    whole = room_for(image_bytes, 3) and (steps + warm) * image_bytes <= 30 * 16 * GiB and not args.ref_sample
+    sample = image_bytes if whole else min(image_bytes, 2 * GiB)
+    gbs, t, logical = time_reference_copy(sample, steps, warm)
     line = {
         "impl": "reference", "metric": METRIC, "value": round(gbs, 4), "unit": "GB/s", "n_gpus": args.gpus,
-        "steps": max(1, args.steps), "warmup": warm, "ms_per_step": round(t * 1e3, 3), "higher_is_better": True,
+        "steps": steps, "warmup": warm, "ms_per_step": round(t * 1e3, 3), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "image_bytes": LLAMA3_8B_PARAMS * 2,
-                   "note": "reference = pkg/gritagent/copy/copy.go restated in C++ (no Go toolchain here); "
-                           "TransferData up + TransferData down + sentinel, tmpfs to tmpfs"},
-        "cpu_baseline": {"value": round(gbs, 4), "unit": "GB/s", "cores": 1, "kind": "port",
-                         "host_cores": cores,
-                         "sample": f"{logical} B CRIU-style dir ({sample >> 30} GiB pages-1.img + metadata files) in "
+        "config": bench_config(world, n_pages),
+        "copied_bytes_per_step": logical, "copied": "the whole image of one rank" if whole else "a bounded sample of the image",
+        "note": "reference = pkg/gritagent/copy/copy.go restated in C++ (no Go toolchain here); TransferData up + "
+                "TransferData down + sentinel, tmpfs to tmpfs; rank 0 only (one agent Job per pod)",
+        "cpu_baseline": {"value": round(gbs, 4), "unit": "GB/s", "cores": 1, "kind": "port", "host_cores": cores,
+                         "sample": f"{logical} B CRIU-style dir ({sample} B pages-1.img + metadata files) in "
                                    f"{tmp_root()}; one file per worker (copy.go:39-51) so the big file runs on 1 thread"},
         "e2e": {"value": round(gbs, 4), "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -210,10 +267,111 @@ def run_reference(args):
     return 0
 
 
-# ----------------------------------------------------------------------------- gritpack arm
+# ----------------------------------------------------------------------------- gritpack arm: images
+def llama_image(torch, dev, n_pages, seed):
+    torch.manual_seed(seed)
+    return torch.empty(n_pages * PAGE // 2, dtype=torch.bfloat16, device=dev).normal_(0, 0.02).view(torch.uint8)
+
+
+def c3_image(torch, ctx, dev, rank, n_pages):
+    """configs[2]: [base weights | LoRA + Adam | workspace | zero slack | host pages], scaled when --pages overrides."""
+    f = n_pages / C3_PAGES
+    base, lora, work, slack = (max(1, int(x * f)) for x in (C3_BASE, C3_LORA, C3_WORK, C3_SLACK))
+    host = n_pages - base - lora - work - slack
+    assert host > 0
+    img = torch.empty(n_pages * PAGE, dtype=torch.uint8, device=dev)
+    g = torch.Generator(device=dev)
+    g.manual_seed(0xBA5E)                                    # the same weights on every rank
+    img[: base * PAGE].view(torch.bfloat16).normal_(0, 0.02, generator=g)
+    g.manual_seed(0x10A0 + rank)
+    o = base * PAGE
+    img[o: o + lora * PAGE].view(torch.float32).normal_(0, 0.01, generator=g)
+    o += lora * PAGE
+    step = 256 << 20                                        # randint makes an int64 temporary: go in pieces
+    for a in range(o, o + work * PAGE, step):
+        b = min(a + step, o + work * PAGE)
+        img[a:b].view(torch.int32).copy_(torch.randint(-2**31, 2**31 - 1, ((b - a) // 4,), dtype=torch.int32, device=dev,
+                                                       generator=g))
+    o += work * PAGE
+    img[o: o + slack * PAGE].zero_()
+    o += slack * PAGE
+    img[o:].copy_(ctx.synth_image(host, seed=0xC0FFEE + rank))
+    layout = {"base": base, "lora_adam": lora, "workspace": work, "zero_slack": slack, "host_c1_mix": host}
+    return img, layout
+
+
+def dirty_copy(torch, image, n_pages, rank):
+    """configs[3]: 5 % of the pages (seeded uniform choice, the same pages on every rank) overwritten with fresh
+    rank-seeded random data."""
+    child = image.clone()
+    g = torch.Generator(device=image.device)
+    g.manual_seed(0xD1127)
+    dirty = torch.randperm(n_pages, device=image.device, generator=g)[: n_pages // 20]
+    g.manual_seed(0xD1127 + 1 + rank)
+    step = 1 << 15
+    v = child.view(n_pages, PAGE)
+    for a in range(0, dirty.numel(), step):
+        idx = dirty[a: a + step]
+        v[idx] = torch.randint(0, 256, (idx.numel(), PAGE), dtype=torch.uint8, device=image.device, generator=g)
+    return child
+
+
+def cross_rank_selftest(torch, dist, ctx, comm, rank, world):
+    """Small images, every result checked by properties on every rank (N > 1, before anything is timed):
+    shared pages become PEER references to the same page of rank 0, the ranked pack (sliced K1 + NCCL exchange inside
+    the library) decides exactly what the stage entry points decide when handed the lower ranks' tables as plain
+    arrays, and a restore that follows the PEER references returns the image bit for bit."""
+    dev = torch.device("cuda", ctx.device)
+    shared = ctx.synth_image(9000, seed=0xBA5E, pct_zero=0, pct_dup=0)
+    sizes = [1000 + 300 * q for q in range(world)]
+    own = ctx.synth_image(sizes[rank], seed=500 + rank, pct_zero=10, pct_dup=10, dup_pool=16)
+    image = torch.cat([shared, own])
+    n = image.numel() // PAGE
+    packed = torch.empty_like(image)
+    out = {}
+    for max_pages in (0, 9000 + sizes[-1]):
+        r = comm.pack(image, packed, max_pages=max_pages)
+        ref = r["ref"]
+        kinds = (ref >> 29) & 7
+        if rank == 0:
+            assert r["stats"]["n_peer"] == 0
+        else:
+            assert int((kinds[:9000] == 4).sum()) == 9000, "shared pages must be PEER references"
+            assert int(((ref[:9000] >> 26) & 7).max()) == 0, "the lowest rank owns a shared page"
+            assert torch.equal(ref[:9000] & ((1 << 26) - 1), torch.arange(9000, device=dev, dtype=torch.int32))
+        # the same decision through the stage entry points, tables moved by torch.distributed
+        crc, h, ref2 = ctx.analyze(image)
+        m = 9000 + sizes[-1]
+        hs = [torch.zeros(m, dtype=torch.int64, device=dev) for _ in range(world)]
+        cs = [torch.zeros(m, dtype=torch.int32, device=dev) for _ in range(world)]
+        hp, cp = torch.zeros(m, dtype=torch.int64, device=dev), torch.zeros(m, dtype=torch.int32, device=dev)
+        hp[:n], cp[:n] = h, crc
+        dist.all_gather(hs, hp)
+        dist.all_gather(cs, cp)
+        peers = [(hs[q][: 9000 + sizes[q]].contiguous(), cs[q][: 9000 + sizes[q]].contiguous()) for q in range(rank)]
+        ctx.dedup(crc, h, ref2, peers=peers)
+        packed2 = torch.empty_like(image)
+        n2 = ctx.compact(image, ref2, packed2)
+        assert n2 == r["stats"]["n_data"] and torch.equal(ref2, ref) and torch.equal(crc, r["crc"])
+        assert torch.equal(packed2[: n2 * PAGE], r["packed"])
+        out = {"n_peer": r["stats"]["n_peer"], "n_data": r["stats"]["n_data"], "n_pages": n}
+    peer_images = []
+    for q in range(world):
+        buf = image if q == rank else torch.empty((9000 + sizes[q]) * PAGE, dtype=torch.uint8, device=dev)
+        comm.broadcast(buf, root=q)
+        if q < rank:
+            peer_images.append(buf)
+    torch.cuda.synchronize()
+    back, st = ctx.restore(r["packed"], r["ref"], r["crc"], peer_images=peer_images)
+    assert st["n_bad"] == 0 and torch.equal(back, image), "selftest: restored image differs"
+    return out
+
+
+# ----------------------------------------------------------------------------- gritpack arm: measurement
 def run_gritpack(args):
     import torch
     import torch.distributed as dist
+    from grit_b200 import dist as gdist
     from grit_b200.buffers import Context
 
     rank = int(os.environ.get("RANK", "0"))
@@ -224,18 +382,14 @@ def run_gritpack(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     ctx = Context(local)
     dev = torch.device("cuda", local)
+    peak, peak_src = measured_peak()
 
-    n_pages = args.pages or (LLAMA3_8B_PARAMS * 2 + PAGE - 1) // PAGE
-    free, _ = torch.cuda.mem_get_info()
-    if free < 3.4 * n_pages * PAGE:
-        raise SystemExit(f"device has {free >> 30} GiB free; the workload needs {3.4 * n_pages * PAGE / 2**30:.0f} GiB")
+    n_pages = pages_for(world, args.pages)
     n_bytes = n_pages * PAGE
-    torch.manual_seed(1234 + rank)
-    image = torch.empty(n_bytes // 2, dtype=torch.bfloat16, device=dev).normal_(0, 0.02).view(torch.uint8)
-    packed = torch.empty(n_bytes, dtype=torch.uint8, device=dev)
-    restored = torch.empty(n_bytes, dtype=torch.uint8, device=dev)
-    meta = (torch.empty(n_pages, dtype=torch.int32, device=dev), torch.empty(n_pages, dtype=torch.int32, device=dev),
-            torch.empty(n_pages, dtype=torch.int64, device=dev))
+    free, _ = torch.cuda.mem_get_info()
+    need = (3.4 if world == 1 else 5.6) * n_bytes
+    if free < need:
+        raise SystemExit(f"device has {free >> 30} GiB free; the workload needs {need / 2**30:.0f} GiB")
 
     def barrier():
         torch.cuda.synchronize()
@@ -243,21 +397,77 @@ def run_gritpack(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def pack_step():
-        """K1 -> [hash all-gather over NCCL when world > 1] -> K2 -> K3."""
+    def timed(fn, reps=5, sync_ranks=False):
+        """CUDA events on the launching (current) stream; with sync_ranks the slowest rank's time."""
+        fn()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier() if sync_ranks else torch.cuda.synchronize()
+        a.record()
+        for _ in range(reps):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        ms = torch.tensor([a.elapsed_time(b) / reps], device=dev)
+        if sync_ranks and world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    # ---- the image of this rank, and (N > 1) the communicator + self-test + the lower ranks' images
+    comm, selftest, layout, peer_images = None, None, None, []
+    if world == 1:
+        image = llama_image(torch, dev, n_pages, 1234)
+    else:
+        comm = gdist.Comm.from_torch_distributed(ctx)
+        selftest = cross_rank_selftest(torch, dist, ctx, comm, rank, world)
+        image, layout = c3_image(torch, ctx, dev, rank, n_pages)
+    packed = torch.empty(n_bytes, dtype=torch.uint8, device=dev)
+    restored = torch.empty(n_bytes, dtype=torch.uint8, device=dev)
+    meta = (torch.empty(n_pages, dtype=torch.int32, device=dev), torch.empty(n_pages, dtype=torch.int32, device=dev),
+            torch.empty(n_pages, dtype=torch.int64, device=dev))
+
+    def pack_step(img=None, parent=None):
+        """K1 -> K2 -> K3; at N > 1 through grit_pack_buffer_ranked: sliced K1 with the NCCL table exchange beside it."""
+        img = image if img is None else img
         if world == 1:
-            return ctx.pack(image, packed=packed, out=meta)
-        from grit_b200 import dist as gdist
-        crc, h, ref = ctx.analyze(image, through=packed)
-        tables = gdist.all_gather_tables(h, crc, counts=[n_pages] * world)   # NCCL over NVLink: 12 B per 4 KiB page
-        ctx.dedup(crc, h, ref, peers=gdist.peers_of(rank, tables))
-        n = ctx.compact(image, ref, packed)
-        return dict(ref=ref, crc=crc, hash=h, packed=packed[: n * PAGE], stats={"n_data": n})
+            return ctx.pack(img, parent=parent, packed=packed, out=meta)
+        return comm.pack(img, packed, parent=parent, max_pages=n_pages, out=meta)
+
+    def stage_peer_images(ref):
+        """Which lower ranks do my PEER references name?  Every rank that anyone needs broadcasts its image
+        (grit_comm_broadcast, outside every timed region); a rank that does not need it receives into scratch."""
+        need_mask = torch.zeros(world, dtype=torch.int32, device=dev)
+        peer = ref[((ref >> 29) & 7) == 4]
+        if peer.numel():
+            need_mask[torch.unique((peer >> 26) & 7).long()] = 1
+        mine = need_mask.clone()
+        dist.all_reduce(need_mask, op=dist.ReduceOp.MAX)
+        imgs = [None] * rank
+        for q in range(world):
+            if not int(need_mask[q]):
+                continue
+            if q == rank:
+                comm.broadcast(image, root=q)
+            elif q < rank and int(mine[q]):
+                imgs[q] = torch.empty(n_bytes, dtype=torch.uint8, device=dev)
+                comm.broadcast(imgs[q], root=q)
+            else:
+                comm.broadcast(restored, root=q)
+        torch.cuda.synchronize()
+        return imgs
+
+    r = pack_step()
+    if world > 1:
+        peer_images = stage_peer_images(r["ref"])
+
+    def restore_step(res=None, parent_image=None):
+        res = r if res is None else res
+        return ctx.restore(res["packed"], res["ref"], res["crc"], parent_image=parent_image, peer_images=peer_images,
+                           out=restored)
 
     def step():
-        r = pack_step()
-        ctx.restore(r["packed"], r["ref"], r["crc"], out=restored)
-        return r
+        res = pack_step()
+        restore_step(res)
+        return res
 
     # ---- value: device-resident, K timed steps, CUDA events, max over ranks
     sampler = ClockSampler(local)
@@ -274,7 +484,7 @@ def run_gritpack(args):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(args.steps):
-        step()
+        r = step()
     e1.record()
     barrier()
     sampler.mark_end()
@@ -286,73 +496,73 @@ def run_gritpack(args):
     ms_per_step = float(ms.item()) / args.steps
     value = world * 2 * n_bytes / (ms_per_step * 1e-3) / 1e9
     assert torch.equal(restored, image), "restored image differs from the source image"
-    stats = r["stats"]
+    stats = dict(r["stats"])
+    mix = torch.tensor([stats[k] for k in ("n_zero", "n_data", "n_dup", "n_parent", "n_peer")], dtype=torch.int64, device=dev)
+    per_rank_mix = None
+    if world > 1:
+        g = [torch.zeros_like(mix) for _ in range(world)]
+        dist.all_gather(g, mix)
+        per_rank_mix = [dict(zip(("n_zero", "n_data", "n_dup", "n_parent", "n_peer"), (int(x) for x in t))) for t in g]
 
-    # ---- per-stage device times (CUDA events on the launching stream), for the roofline
-    def timed(fn, reps=5):
-        fn()
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        torch.cuda.synchronize()
-        a.record()
-        for _ in range(reps):
-            fn()
-        b.record()
-        torch.cuda.synchronize()
-        return a.elapsed_time(b) / reps
-
-    # (1) the kernels of the timed step itself: grit_pack_buffer brackets K1, K2, K3 with CUDA events on the
-    #     launching stream (stats.stage_ms); restore is one kernel
-    peak, peak_src = measured_peak()
-    if world == 1:
-        acc, reps = [0.0, 0.0, 0.0], 5
-        for _ in range(reps + 1):
-            r = ctx.pack(image, packed=packed, out=meta)
-            if _:
-                acc = [x + y for x, y in zip(acc, r["stats"]["stage_ms"])]
-        k1_ms, k2_ms, k3_ms = (x / reps for x in acc)
-        through = bool(r["stats"]["wrote_through"])
-    else:
-        r = pack_step()
-        k1_ms = timed(lambda: ctx.analyze(image, through=packed))
-        k2_ms = k3_ms = None
-        through = True   # rank-seeded dense images: K1 writes through, K3 finds the pages in place
-    n_data = int(r["stats"]["n_data"])
+    # ---- per-stage device times of the timed step's own kernels (grit_pack_buffer* bracket K1 | K2 | K3 with CUDA
+    #      events on the launching stream: stats.stage_ms); restore is one kernel
+    acc, reps = [0.0, 0.0, 0.0], 5
+    for i in range(reps + 1):
+        rr = pack_step()
+        if i:
+            acc = [x + y for x, y in zip(acc, rr["stats"]["stage_ms"])]
+    k1_ms, k2_ms, k3_ms = (x / reps for x in acc)
+    through = bool(rr["stats"]["wrote_through"])
+    n_data = int(rr["stats"]["n_data"])
     U = n_data * PAGE
-    t_restore = timed(lambda: ctx.restore(r["packed"], r["ref"], r["crc"], out=restored))
-    t_pack = timed(lambda: pack_step())
+    t_restore = timed(restore_step, sync_ranks=True)
+    t_pack = timed(pack_step, sync_ranks=True)
+    # pages K1' stored to their own slots: all of them for a dense image, the prefix in front of the first zero page
+    # otherwise (the configs[2] image: everything before the allocator slack)
+    wt_pages = 0
+    if through:
+        wt_pages = n_pages if world == 1 else layout["base"] + layout["lora_adam"] + layout["workspace"]
     stages = {
         "k_analyze_through" if through else "k_analyze": {
-            "ms": k1_ms, "alg_bytes": n_bytes + (U if through else 0) + 16 * n_pages,
-            "does": "CRC-32C + zero + hash64" + (", pages stored to their own slots (dense image)" if through else "")},
-        "k_restore": {"ms": t_restore, "alg_bytes": U + n_bytes + 8 * n_pages, "does": "scatter + CRC-32C verify"},
+            "ms": k1_ms, "alg_bytes": n_bytes + wt_pages * PAGE + 16 * n_pages,
+            "does": "CRC-32C + zero + hash64" + (", pages stored to their own slots (dense prefix)" if through else "")
+                    + (", in slices with the NCCL table all-gather beside it" if world > 1 else "")},
+        "k_restore": {"ms": t_restore, "alg_bytes": U + n_bytes + 8 * n_pages, "does": "scatter + CRC-32C verify"
+                      + (" (PEER pages read from the staged image of rank 0)" if world > 1 else "")},
+        "dedup (k_table_insert + k_table_probe_lists + k_resolve)": {
+            "ms": k2_ms, "alg_bytes": 32 * n_pages,
+            "does": "hash table + references" + ("; includes waiting for the last slice of the exchange" if world > 1 else "")},
+        "k_compact": {"ms": k3_ms, "alg_bytes": 2 * (n_data - min(wt_pages, n_data)) * PAGE + 8 * n_pages,
+                      "does": "scan + slots + copy of the stored pages that are not in place"},
     }
-    if k2_ms is not None:
-        stages["dedup (k_table_insert + k_resolve)"] = {"ms": k2_ms, "alg_bytes": 32 * n_pages, "does": "hash table + references"}
-        stages["k_compact"] = {"ms": k3_ms, "alg_bytes": (0 if through else 2 * U) + 8 * n_pages,
-                               "does": "scan + slots" + ("; pages already in place" if through else " + copy of the stored pages")}
-    # (2) for reference, the plain three-kernel pack through the stage entry points (what runs for images with
-    #     zero pages, parents or peers)
-    ref, crc, h = meta
-    t_analyze = timed(lambda: ctx.analyze(image))
-    crc_a, h_a, ref_a = ctx.analyze(image)
-    ref_work = ref_a.clone()
+    if world > 1 and rank == 0:
+        for s in stages.values():
+            s["rank"] = 0
 
-    def dedup_only():
-        ref_work.copy_(ref_a)
-        ctx.dedup(crc_a, h_a, ref_work)
-    t_copy = timed(lambda: ref_work.copy_(ref_a))
-    t_dedup = max(timed(dedup_only) - t_copy, 0.0)
-    dedup_only()
-    ref_keep = ref_work.clone()
+    # ---- for reference, the plain three-kernel pack through the stage entry points (N = 1)
+    plain = None
+    if world == 1:
+        t_analyze = timed(lambda: ctx.analyze(image))
+        crc_a, h_a, ref_a = ctx.analyze(image)
+        ref_work = ref_a.clone()
 
-    def compact_only():
-        ref_work.copy_(ref_keep)
-        ctx.compact(image, ref_work, packed)
-    t_compact = max(timed(compact_only) - t_copy, 0.0)
-    plain = {"k_analyze": {"ms": t_analyze, "alg_bytes": n_bytes + 16 * n_pages},
-             "dedup": {"ms": t_dedup, "alg_bytes": 32 * n_pages},
-             "k_compact": {"ms": t_compact, "alg_bytes": 2 * U + 8 * n_pages}}
-    for grp_ in (stages, plain):
+        def dedup_only():
+            ref_work.copy_(ref_a)
+            ctx.dedup(crc_a, h_a, ref_work)
+        t_copy = timed(lambda: ref_work.copy_(ref_a))
+        t_dedup = max(timed(dedup_only) - t_copy, 0.0)
+        dedup_only()
+        ref_keep = ref_work.clone()
+
+        def compact_only():
+            ref_work.copy_(ref_keep)
+            ctx.compact(image, ref_work, packed)
+        t_compact = max(timed(compact_only) - t_copy, 0.0)
+        plain = {"k_analyze": {"ms": t_analyze, "alg_bytes": n_bytes + 16 * n_pages},
+                 "dedup": {"ms": t_dedup, "alg_bytes": 32 * n_pages},
+                 "k_compact": {"ms": t_compact, "alg_bytes": 2 * U + 8 * n_pages}}
+        del crc_a, h_a, ref_a, ref_work, ref_keep
+    for grp_ in (stages, plain or {}):
         for s in grp_.values():
             s["gbs"] = round(s["alg_bytes"] / (s["ms"] * 1e-3) / 1e9, 1) if s["ms"] and s["ms"] > 0 else None
             s["frac"] = round(s["gbs"] / peak, 4) if s["gbs"] else None
@@ -370,24 +580,26 @@ def run_gritpack(args):
                 "traffic_source": traffic_src, "alg_bytes": stages[dom]["alg_bytes"], "stages": stages,
                 "plain_three_kernel_pack": plain,
                 "pack_whole": {"ms": round(t_pack, 4), "alg_bytes": n_bytes + U + 16 * n_pages,
-                               "frac": round((n_bytes + U + 16 * n_pages) / (t_pack * 1e-3) / 1e9 / peak, 4)}}
+                               "frac": round((n_bytes + U + 16 * n_pages) / (t_pack * 1e-3) / 1e9 / peak, 4),
+                               "note": "slowest rank" if world > 1 else None},
+                "restore_whole": {"ms": round(t_restore, 4), "alg_bytes": n_bytes + U + 8 * n_pages,
+                                  "frac": round((n_bytes + U + 8 * n_pages) / (t_restore * 1e-3) / 1e9 / peak, 4)}}
 
-    # ---- the same kernels on the other page mixes of BASELINE.json (not the headline; parity-tested in tests/)
+    # ---- the other page mixes of BASELINE.json (not the headline; parity-tested in tests/)
     other = None
-    if world == 1 and not args.no_extra:
+    if not args.no_extra:
         other = {}
-        peak = measured_peak()[0]
-        full = ctx.pack(image, packed=packed, out=meta)
+        full = pack_step()
         parent_tab = (full["hash"].clone(), full["crc"].clone())
-        # config 4: 5 % of the pages dirtied since the previous checkpoint, packed against its hash table
-        child = image.clone()
-        g = torch.Generator(device=dev).manual_seed(0xD1127)
-        dirty = torch.randperm(n_pages, device=dev, generator=g)[: n_pages // 20]
-        child.view(n_pages, PAGE)[dirty] = torch.randint(0, 256, (dirty.numel(), PAGE), dtype=torch.uint8, device=dev,
-                                                         generator=g)
-        ri = ctx.pack(child, parent=parent_tab, packed=packed)
-        t_p = timed(lambda: ctx.pack(child, parent=parent_tab, packed=packed))
-        t_r = timed(lambda: ctx.restore(ri["packed"], ri["ref"], ri["crc"], parent_image=image, out=restored))
+        # configs[3]: 5 % of the pages dirtied since the previous checkpoint, packed against its hash table (and, at
+        # N > 1, against the lower ranks: dirtied weight pages differ per rank here, so they are stored)
+        child = dirty_copy(torch, image, n_pages, rank)
+        ri = pack_step(child, parent=parent_tab)
+        ri = {k: (v.clone() if k in ("ref", "crc") else v) for k, v in ri.items()}
+        t_p = timed(lambda: pack_step(child, parent=parent_tab), sync_ranks=True)
+        packed_i = ri["packed"].clone()
+        ri["packed"] = packed_i
+        t_r = timed(lambda: restore_step(ri, parent_image=image), sync_ranks=True)
         assert torch.equal(restored, child), "incremental restore differs"
         Ui = int(ri["stats"]["n_data"]) * PAGE
         other["incremental_5pct_dirty"] = {
@@ -395,21 +607,48 @@ def run_gritpack(args):
             "pack_ms": round(t_p, 3), "restore_ms": round(t_r, 3),
             "pack_frac": round((n_bytes + Ui + 16 * n_pages) / (t_p * 1e-3) / 1e9 / peak, 4),
             "restore_frac": round((n_bytes + n_bytes + 8 * n_pages) / (t_r * 1e-3) / 1e9 / peak, 4),
-            "note": "restore reads the unchanged pages from the parent image in HBM"}
-        del child
-        # config 1 mix: 10 % zero pages, 15 % duplicates from a 1024-page pool, 75 % unique
-        mix = ctx.synth_image(n_pages, seed=0xC0FFEE)
-        rm = ctx.pack(mix, packed=packed)
-        t_p = timed(lambda: ctx.pack(mix, packed=packed))
-        t_r = timed(lambda: ctx.restore(rm["packed"], rm["ref"], rm["crc"], out=restored))
-        assert torch.equal(restored, mix), "C1-mix restore differs"
-        Um = int(rm["stats"]["n_data"]) * PAGE
-        other["c1_mix_10zero_15dup"] = {
-            "page_mix": {k: int(v) for k, v in rm["stats"].items() if k.startswith("n_")},
-            "pack_ms": round(t_p, 3), "restore_ms": round(t_r, 3),
-            "pack_frac": round((n_bytes + Um + 16 * n_pages) / (t_p * 1e-3) / 1e9 / peak, 4),
-            "restore_frac": round((Um + n_bytes + 8 * n_pages) / (t_r * 1e-3) / 1e9 / peak, 4)}
-        del mix
+            "note": "restore reads the unchanged pages from the parent image in HBM; times are the slowest rank's"}
+        del child, packed_i, ri
+        if world == 1:
+            # configs[0] mix: 10 % zero pages, 15 % duplicates from a 1024-page pool, 75 % unique
+            mix_img = ctx.synth_image(n_pages, seed=0xC0FFEE)
+            rm = ctx.pack(mix_img, packed=packed)
+            t_p = timed(lambda: ctx.pack(mix_img, packed=packed))
+            sm = [0.0, 0.0, 0.0]
+            for _ in range(3):
+                sm = [x + y / 3 for x, y in zip(sm, ctx.pack(mix_img, packed=packed)["stats"]["stage_ms"])]
+            t_r = timed(lambda: ctx.restore(rm["packed"], rm["ref"], rm["crc"], out=restored))
+            assert torch.equal(restored, mix_img), "C1-mix restore differs"
+            Um = int(rm["stats"]["n_data"]) * PAGE
+            other["c1_mix_10zero_15dup"] = {
+                "page_mix": {k: int(v) for k, v in rm["stats"].items() if k.startswith("n_")},
+                "pack_ms": round(t_p, 3), "restore_ms": round(t_r, 3), "stage_ms": [round(x, 3) for x in sm],
+                "pack_frac": round((n_bytes + Um + 16 * n_pages) / (t_p * 1e-3) / 1e9 / peak, 4),
+                "restore_frac": round((Um + n_bytes + 8 * n_pages) / (t_r * 1e-3) / 1e9 / peak, 4)}
+            del mix_img, rm
+        else:
+            # round-1 comparability: rank-seeded dense llama-sized images (no PEER references arise) through the
+            # same ranked pack -- the weak-scaling figure of the exchange itself
+            n_l = pages_for(1)
+            if torch.cuda.mem_get_info()[0] > 3.3 * n_l * PAGE:
+                del packed, restored
+                torch.cuda.empty_cache()
+                img_l = llama_image(torch, dev, n_l, 1234 + rank)
+                packed_l = torch.empty(n_l * PAGE, dtype=torch.uint8, device=dev)
+                out_l = torch.empty(n_l * PAGE, dtype=torch.uint8, device=dev)
+
+                def step_l():
+                    q = comm.pack(img_l, packed_l, max_pages=n_l)
+                    ctx.restore(q["packed"], q["ref"], q["crc"], out=out_l)
+                t_l = timed(step_l, reps=10, sync_ranks=True)
+                assert torch.equal(out_l, img_l)
+                other["llama3_dense_rank_seeded"] = {
+                    "ms_per_step": round(t_l, 4), "value": round(world * 2 * n_l * PAGE / (t_l * 1e-3) / 1e9, 1),
+                    "note": "the N = 1 workload with a different seed per rank, packed through grit_pack_buffer_ranked"}
+                del img_l, packed_l, out_l
+                torch.cuda.empty_cache()
+                packed = torch.empty(n_bytes, dtype=torch.uint8, device=dev)
+                restored = torch.empty(n_bytes, dtype=torch.uint8, device=dev)
         torch.cuda.empty_cache()
 
     # ---- host link peaks of this box, measured now: the binding roofline of the e2e number
@@ -475,12 +714,18 @@ def run_gritpack(args):
         hu = int(hr["stats"]["n_data"]) * PAGE
         e2e = {"value": round(world * 2 * hb / (float(dt.item()) / k_e2e) / 1e9, 3), "unit": "GB/s",
                "h2d_bytes_per_step": hb + hu + 8 * e2e_pages, "d2h_bytes_per_step": hu + hb + 16 * e2e_pages,
-               "steps": k_e2e, "image_bytes": hb, "link": link,
+               "steps": k_e2e, "image_bytes": hb, "stored_bytes": hu, "link": link,
                "frac_of_link": round(2 * hb / (float(dt.item()) / k_e2e) / 1e9 / link["both_gbs_per_direction"], 3),
-               "bound": "PCIe Gen5 x16, both directions busy: each direction carries the image once per pack and "
-                        "once per restore",
-               "api": "grit_pack_host + grit_restore_host (pinned host buffers, 64 MiB chunks, 3 streams)"}
+               "bound": "PCIe Gen5 x16, both directions busy: a pack carries the image up and the stored pages down, a "
+                        "restore the stored pages up and the image down",
+               "api": "grit_pack_host + grit_restore_host (pinned host buffers, 64 MiB chunks, 3 streams)"
+                      + ("; each rank packs its own image, no cross-rank references on this path" if world > 1 else "")}
         del h_img, h_packed, h_out
+
+    # ---- e2e_dir: the reference's own boundary (TransferData on directories), N = 1
+    e2e_dir = None
+    if rank == 0 and world == 1 and not args.no_dir:
+        e2e_dir = measure_e2e_dir(torch, ctx, image, n_pages)
 
     # ---- CPU baseline on this box's host cores (rank 0, N=1 only): bounded samples
     cpu_baseline = None
@@ -500,20 +745,180 @@ def run_gritpack(args):
             "metric": METRIC, "value": round(value, 2), "unit": "GB/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": round(ms_per_step, 4), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "image_bytes_per_gpu": n_bytes, "pages_per_gpu": n_pages,
-                       "seed": 1234, "l2": "inputs (16 GB per step) are larger than the 126 MB L2; no flush needed",
-                       "cross_rank": "hash64+crc all-gather over NCCL before dedup" if world > 1 else "none (1 GPU)",
-                       "page_mix": {k: int(v) for k, v in stats.items() if k.startswith("n_")}},
+            "config": bench_config(world, n_pages),
+            "page_mix": {k: int(v) for k, v in stats.items() if k.startswith("n_")},
+            "page_mix_per_rank": per_rank_mix, "image_layout_pages": layout,
+            "cross_rank": ("grit_pack_buffer_ranked: (hash64, crc) all-gather over NCCL inside libgritpack.so, sliced "
+                           "beside K1; PEER pages restored from the owner's image staged in local HBM before the "
+                           "timed region (grit_comm_broadcast)") if world > 1 else "none (1 GPU)",
+            "selftest": ({"passed": True} | selftest) if selftest else None,
             "pack_gbs": round(world * n_bytes / (t_pack * 1e-3) / 1e9, 1),
             "restore_gbs": round(world * n_bytes / (t_restore * 1e-3) / 1e9, 1),
-            "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "other_mixes": other,
+            "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "e2e_dir": e2e_dir, "other_mixes": other,
             "gpu_launches": int(launches),
             "clocks": clocks, "bit_exact": True,
         }
         print(json.dumps(line), file=RESULT, flush=True)
+    if comm is not None:
+        comm.close()
     if world > 1:
         dist.destroy_process_group()
     return 0
+
+
+# ----------------------------------------------------------------------------- e2e_dir
+def _write_tensor(path, t, mode=0o600):
+    with open(path, "wb") as f:
+        step = 1 << 30
+        for a in range(0, t.numel(), step):
+            t[a: a + step].cpu().numpy().tofile(f)
+    os.chmod(path, mode)
+
+
+def _small_criu_files(torch, ck, seed):
+    """The small opaque files of a CRIU image directory (sizes that are no page multiples)."""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    names = ["inventory.img", "files.img", "fs-1.img", "ids-1.img", "mm-1.img", "core-1.img", "core-2.img", "pagemap-1.img",
+             "pagemap-2.img", "fdinfo-2.img", "fdinfo-3.img", "pstree.img", "seccomp.img", "timens-0.img", "tty-info.img",
+             "utsns-12.img", "ipcns-var-11.img", "mountpoints-13.img", "netdev-10.img", "ifaddr-10.img", "route-10.img",
+             "cgroup.img", "stats-dump", "descriptors.json"]
+    sizes = np.exp(rng.uniform(np.log(64), np.log(2 << 20), len(names))).astype(np.int64) | 1
+    for n, sz in zip(names, sizes):
+        with open(os.path.join(ck, n), "wb") as f:
+            f.write(rng.integers(0, 256, int(sz), dtype=np.uint8).tobytes())
+
+
+def _build_c1(torch, ctx, root):
+    """the 1 GiB CRIU image dir (pages-1/2/3.img with the 10/15/75 class mix, 24 small files,
+    rootfs-diff.tar, logs)."""
+    import numpy as np
+    ck = os.path.join(root, "main", "checkpoint")
+    os.makedirs(ck)
+    _small_criu_files(torch, ck, 0xC0FFEE)
+    for name, mib, k in (("pages-1.img", 768, 1), ("pages-2.img", 192, 2), ("pages-3.img", 47, 3)):
+        _write_tensor(os.path.join(ck, name), ctx.synth_image((mib << 20) // PAGE, seed=0xC0FFEE + k))
+    rng = np.random.default_rng(5)
+    with open(os.path.join(root, "main", "rootfs-diff.tar"), "wb") as f:
+        f.write(rng.integers(0, 256, 16 << 20, dtype=np.uint8).tobytes())
+    with open(os.path.join(root, "main", "container.log"), "wb") as f:
+        f.write((b"2025-02-21T08:00:00.000000000Z stdout F step 100 loss 1.2345\n" * 4000)[: 200 * 1024])
+    with open(os.path.join(root, "main", "dump.log"), "wb") as f:
+        f.write((b"(00.012345) Dumping pages for task 1234\n" * 1200)[: 40 * 1024])
+
+
+def _same_tree(a, b):
+    """Same relative paths, sizes and modes; bytes compared in full below 2 GiB per file, at the head, the middle and
+    the tail (64 MiB each) above."""
+    for d, _, fs in os.walk(a):
+        for f in fs:
+            pa = os.path.join(d, f)
+            pb = os.path.join(b, os.path.relpath(pa, a))
+            sa, sb = os.stat(pa), os.stat(pb)
+            if sa.st_size != sb.st_size or (sa.st_mode & 0o7777) != (sb.st_mode & 0o7777):
+                return False
+            spans = [(0, sa.st_size)] if sa.st_size < 2 * GiB else [(0, 64 << 20), (sa.st_size // 2, 64 << 20),
+                                                                    (sa.st_size - (64 << 20), 64 << 20)]
+            with open(pa, "rb") as fa, open(pb, "rb") as fb:
+                for off, n in spans:
+                    fa.seek(off)
+                    fb.seek(off)
+                    left = n
+                    while left > 0:
+                        x, y = fa.read(min(left, 16 << 20)), fb.read(min(left, 16 << 20))
+                        if x != y:
+                            return False
+                        if not x:
+                            break
+                        left -= len(x)
+    return True
+
+
+def measure_e2e_dir(torch, ctx, image, n_pages):
+    """grit_pack_dir + grit_restore_dir + sentinel against TransferData + TransferData + sentinel (copy.go restated) on
+    the same trees in the same tmpfs.  warm: in this process (CUDA runtime up, the library creates and destroys its
+    own context per call).  cold: a fresh grit-agent process per direction, everything it pays included."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as O
+    from grit_b200 import copy
+    agent = os.path.join(ROOT, "grit_b200", "csrc", "grit-agent")
+    n_bytes = n_pages * PAGE
+    big = n_bytes if room_for(n_bytes, 3.3) else min(n_bytes, 4 * GiB)
+    out = {"where": tmp_root(), "host_cores": os.cpu_count()}
+
+    def build_giant(root):
+        ck = os.path.join(root, "main", "checkpoint")
+        os.makedirs(ck)
+        _small_criu_files(torch, ck, 7)
+        _write_tensor(os.path.join(ck, "pages-1.img"), image[:big])
+
+    def build_eleven(root):
+        _build_c1(torch, ctx, root)
+        for k in range(11):
+            _write_tensor(os.path.join(root, "main", "checkpoint", f"pages-{10 + k}.img"), image[k * GiB:(k + 1) * GiB])
+
+    trees = [("one_giant_pages_img", build_giant), ("c1_1gib_criu_dir", lambda r: _build_c1(torch, ctx, r))]
+    if room_for(13 * GiB, 3.3) and n_bytes >= 11 * GiB:
+        trees.append(("c1_plus_eleven_1gib_files", build_eleven))
+    for name, build in trees:
+        base = tempfile.mkdtemp(prefix="gritdir_", dir=tmp_root())
+        try:
+            src, pv, back = (os.path.join(base, x) for x in ("host", "pv", "back"))
+            build(src)
+            total = tree_bytes(src)
+            res = {"tree_bytes": total, "files": sum(len(fs) for _, _, fs in os.walk(src))}
+
+            def clean():
+                shutil.rmtree(pv, ignore_errors=True)
+                shutil.rmtree(back, ignore_errors=True)
+            best = None
+            for rep in range(2):
+                t0 = time.perf_counter()
+                assert O.transfer_data(src, pv)[0] == 0
+                t1 = time.perf_counter()
+                assert O.transfer_data(pv, back)[0] == 0 and O.create_sentinel_file(back, "download-state") == 0
+                t2 = time.perf_counter()
+                if best is None or t2 - t0 < sum(best):
+                    best = (t1 - t0, t2 - t1)
+                clean()
+            res["reference"] = {"up_s": round(best[0], 3), "down_s": round(best[1], 3)}
+            ref_total = sum(best)
+            best, stored = None, None
+            for rep in range(2):
+                t0 = time.perf_counter()
+                st = copy.TransferData(src, pv, copy.UPLOAD)
+                t1 = time.perf_counter()
+                copy.TransferData(pv, back, copy.DOWNLOAD)
+                copy.CreateSentinelFile(back, "download-state")
+                t2 = time.perf_counter()
+                if best is None or t2 - t0 < sum(best):
+                    best = (t1 - t0, t2 - t1)
+                stored = st["bytes_stored"]
+                if rep == 0:
+                    os.remove(os.path.join(back, "download-state"))
+                    res["restored_tree_identical"] = _same_tree(src, back)
+                clean()
+            res["gritpack_warm"] = {"up_s": round(best[0], 3), "down_s": round(best[1], 3), "stored_bytes": stored}
+            res["ratio_warm"] = round(ref_total / sum(best), 3)
+            if os.path.exists(agent):
+                t0 = time.perf_counter()
+                r1 = subprocess.run([agent, "--action", "checkpoint", "--src-dir", src, "--dst-dir", pv],
+                                    stdout=subprocess.DEVNULL, stderr=subprocess.PIPE)
+                t1 = time.perf_counter()
+                r2 = subprocess.run([agent, "--action", "restore", "--src-dir", pv, "--dst-dir", back],
+                                    stdout=subprocess.DEVNULL, stderr=subprocess.PIPE)
+                t2 = time.perf_counter()
+                assert r1.returncode == 0 and r2.returncode == 0, (r1.stderr, r2.stderr)
+                res["gritpack_cold"] = {"up_s": round(t1 - t0, 3), "down_s": round(t2 - t1, 3),
+                                        "how": "a fresh grit-agent process per direction (CUDA context creation inside)"}
+                res["ratio_cold"] = round(ref_total / (t2 - t0), 3)
+                clean()
+            res["gbs"] = {"reference": round(2 * total / ref_total / 1e9, 2),
+                          "gritpack_warm": round(2 * total / sum(best) / 1e9, 2)}
+            out[name] = res
+        finally:
+            shutil.rmtree(base, ignore_errors=True)
+    return out
 
 
 RESULT = sys.stdout
@@ -534,7 +939,9 @@ def main():
     ap.add_argument("--pages", type=int, default=0, help="override pages per GPU (debug only; invalid as a bench number)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-dir", action="store_true", help="skip the directory-level legs")
     ap.add_argument("--no-extra", action="store_true", help="skip the other page mixes")
+    ap.add_argument("--ref-sample", action="store_true", help="reference arm: copy a 2 GiB sample even if the image fits")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

@@ -464,7 +464,9 @@ k_table_insert(DedupTable t, const unsigned long long* __restrict__ hash, const 
       unsigned long long k = t.keys[s];
       if (k == 0ull) k = atomicCAS(&t.keys[s], 0ull, h);
       if (k == 0ull || k == h) {
-        atomicMin(&t.vals[s], v);
+        // a much-repeated page (a pool of identical buffers) sends hundreds of pages to one slot: only a value
+        // that lowers the owner is worth an atomic, and the plain read costs a hit in L2
+        if (k == 0ull || __ldcg(&t.vals[s]) > v) atomicMin(&t.vals[s], v);
         break;
       }
     }
@@ -486,7 +488,8 @@ k_table_probe_lists(DedupTable t, ProbeLists lists) {
     for (uint64_t s = table_home(h, t.mask);; s = (s + 1) & t.mask) {
       const unsigned long long k = t.keys[s];
       if (k == h) {
-        atomicMin(&t.vals[s], origin << 26 | (uint32_t)i);
+        const uint32_t v = origin << 26 | (uint32_t)i;
+        if (__ldcg(&t.vals[s]) > v) atomicMin(&t.vals[s], v);
         break;
       }
       if (k == 0ull) break;
