@@ -67,6 +67,7 @@ SYMBOLS = {
     "grit_ctx_create": (_I, [_I, C.POINTER(_P)] + _ERR),
     "grit_ctx_destroy": (None, [_P]),
     "grit_ctx_launches": (_U64, [_P]),
+    "grit_warmup": (_I, [_I]),
     "grit_analyze_pages": (_I, [_P, _P, _U64, _P, _P, _P, _P] + _ERR),
     "grit_analyze_pages_through": (_I, [_P, _P, _U64, _P, _P, _P, _P, _U64, _P] + _ERR),
     "grit_dedup_pages": (_I, [_P, _U64, _P, _P, _P, C.POINTER(Table), C.POINTER(Table), _U32, _P] + _ERR),

@@ -302,6 +302,13 @@ void grit_ctx_destroy(grit_ctx* ctx) {
   delete ctx;
 }
 
+int grit_warmup(int device) {
+  int n_dev = 0;
+  if (cudaGetDeviceCount(&n_dev) != cudaSuccess || device < 0 || device >= n_dev) return GRIT_ECUDA;
+  if (cudaSetDevice(device) != cudaSuccess || cudaFree(nullptr) != cudaSuccess) return GRIT_ECUDA;  // primary context
+  return configure_kernels() == cudaSuccess ? GRIT_OK : GRIT_ECUDA;                                   // loads the module
+}
+
 uint64_t grit_ctx_launches(const grit_ctx* ctx) { return ctx ? ctx->launches : 0; }
 
 int grit_analyze_pages(grit_ctx* ctx, const void* d_image, uint64_t n_pages, uint32_t* d_crc, uint64_t* d_hash,

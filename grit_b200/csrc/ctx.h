@@ -38,7 +38,7 @@ struct grit_ctx {
     void* p = nullptr;
     size_t cap = 0;
   };
-  Buf dev[48], pin[20];
+  Buf dev[48], pin[32];
 };
 
 namespace grit {
@@ -79,8 +79,9 @@ int ctx_dev(grit_ctx* ctx, int id, size_t bytes, void** out, char* err, size_t e
 int ctx_pin(grit_ctx* ctx, int id, size_t bytes, void** out, char* err, size_t errlen);
 enum DevBuf { kDevIn0 = 0, kDevOut0 = 3, kDevRef = 6, kDevCrc, kDevHash, kDevParentHash, kDevParentCrc,
               kDevRPacked, kDevRRef, kDevRCrc, kDevROut0 = 14, kDevRParent = 17,
-              kDevPeerHash0 = 18 /* ..25 */, kDevPeerCrc0 = 26 /* ..33 */, kDevCommHash = 34, kDevCommCrc, kDevCommPad };
-enum PinBuf { kPinIn0 = 0, kPinOut0 = 3, kPinCounts = 6, kPinMeta0 = 7, kPinRStageOut0 = 10, kPinRStageIn0 = 13 /* ..15 */ };
+              kDevPeerHash0 = 18 /* ..25 */, kDevPeerCrc0 = 26 /* ..33 */, kDevCommHash = 34, kDevCommCrc, kDevCommPad, kDevROutX0 = 37 /* ..41 */ };
+enum PinBuf { kPinIn0 = 0, kPinOut0 = 3, kPinCounts = 6, kPinMeta0 = 7, kPinRStageOut0 = 10, kPinRStageIn0 = 13 /* ..15 */,
+              kPinRStageOutX0 = 16 /* ..20 */ };
 bool write_through_pack();  // false with GRITPACK_WRITE_THROUGH=0
 bool staged_pack();  // true unless GRITPACK_FUSED=1 selects the experimental single-pass pack kernel
 

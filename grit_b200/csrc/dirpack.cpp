@@ -559,7 +559,8 @@ struct PageStore {
 struct Opts {
   int device = 0;
   bool verify = true;
-  unsigned io_threads = 8;
+  unsigned io_threads = std::min(16u, std::max(8u, std::thread::hardware_concurrency()));
+  int lanes = 4;             // download of a big tree: interleaved runs of the page range (GRITPACK_LANES)
   uint64_t chunk_pages = 0;  // 0: chosen from the image size
   std::string parent;
   uint32_t n_peers = 0;
@@ -581,6 +582,8 @@ Opts read_opts(const grit_opts* o) {
   r.device = o->device;
   r.verify = o->verify != 0;
   if (o->io_threads) r.io_threads = o->io_threads;
+  else if (const char* e = getenv("GRITPACK_IO_THREADS")) r.io_threads = std::max(1, atoi(e));
+  if (const char* e = getenv("GRITPACK_LANES")) r.lanes = std::max(1, atoi(e));
   if (o->chunk_bytes >= (1u << 20)) r.chunk_pages = o->chunk_bytes / kPage;
   if (o->parent_dir) r.parent = o->parent_dir;
   if (o->struct_size >= sizeof(grit_opts) && o->n_peers && o->peer_tables && o->peer_dirs) {
@@ -1002,7 +1005,9 @@ int restore_or_verify(const char* src_dir, const char* dst_dir, const grit_opts*
     bool joined = true;
     int rc = GRIT_OK;
     std::string msg;
+    std::mutex mu;  // several writer threads may arrive at once
     int wait() {
+      std::lock_guard<std::mutex> l(mu);
       if (!joined) th.join();
       joined = true;
       return rc;
@@ -1067,23 +1072,36 @@ int restore_or_verify(const char* src_dir, const char* dst_dir, const grit_opts*
   io.read_packed = [&](uint64_t s0, uint64_t n, void* dstbuf) -> int {  // reader thread; split over the I/O threads
     return store.io(s0, n, static_cast<char*>(dstbuf), &pool, false);
   };
-  io.write_out = [&](uint64_t p0, uint64_t p1, const void* srcbuf) -> int {
+  std::mutex msg_mu;
+  io.write_out = [&](uint64_t p0, uint64_t p1, const void* srcbuf) -> int {  // writer threads, several at a time
     if (!writing) return 0;  // verify only: the CRC check happened on the GPU, the bytes are dropped
     std::vector<Piece> pieces;
-    if (int rc = skeleton.wait()) return msg = skeleton.msg, rc;
-    pieces_for(files, p0, p1, const_cast<char*>(static_cast<const char*>(srcbuf)), piece_bytes_for(p1 - p0, o.io_threads), &pieces);
-    return for_pieces(&pool, pieces, &msg, [&](const Piece& p, std::string* e) {
-      if (char* base = maps.at[p.e - m.entries.data()])
-        memcpy(base + p.file_off, p.buf, p.len);
-      else
-        write_piece(dst, p, e);
-    });
+    std::string local;
+    int rc = skeleton.wait();
+    if (rc) local = skeleton.msg;
+    if (!rc) {
+      pieces_for(files, p0, p1, const_cast<char*>(static_cast<const char*>(srcbuf)), piece_bytes_for(p1 - p0, o.io_threads), &pieces);
+      rc = for_pieces(&pool, pieces, &local, [&](const Piece& p, std::string* e) {
+        if (char* base = maps.at[p.e - m.entries.data()])
+          memcpy(base + p.file_off, p.buf, p.len);
+        else
+          write_piece(dst, p, e);
+      });
+    }
+    if (rc) {
+      std::lock_guard<std::mutex> l(msg_mu);
+      if (msg.empty()) msg = local;
+    }
+    return rc;
   };
   grit_restore_stats rs{};
   {
     std::lock_guard<std::mutex> g(ctx->mu);
+    // a big tree is restored in interleaved runs of its page range, several destination files being written at once
+    const bool big = writing && m.n_pages * kPage >= (2ull << 30);
     const int rc = restore_stream(ctx, io, m.n_slots, ref.data(), crc.data(), m.n_pages, d_parent, parent_pages, true,
-                                  o.verify, o.chunk_for(m.n_pages), &rs, &st.h2d_bytes, &st.d2h_bytes, err, errlen, &peer_imgs);
+                                  o.verify, o.chunk_for(m.n_pages), &rs, &st.h2d_bytes, &st.d2h_bytes, err, errlen, &peer_imgs,
+                                  big ? o.lanes : 1, big ? 5 : kPipeDepth);
     st.n_bad += rs.n_bad;
     if (rc) {
       if (!msg.empty() && err && errlen) snprintf(err, errlen, "%s", msg.c_str());

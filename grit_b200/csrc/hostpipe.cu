@@ -246,13 +246,17 @@ int PackStream::finish(grit_pack_stats* stats, char* err, size_t errlen) {
 }
 
 // ------------------------------------------------------------------ restore
-// The packed pages are uploaded once and stay resident (slots are referenced in
-// page order, duplicates point backwards), output chunks are restored and
-// downloaded behind the upload front.
+// The packed pages are uploaded once and stay resident; output chunks are restored and downloaded behind the
+// upload.  Output chunks are taken in `lanes` interleaved runs of the page range (lane 0's first chunk, lane 1's
+// first chunk, ...): with callbacks, several writer threads then have chunks of different destination files in
+// hand at the same time (a file system takes a writer or two per file, a tree of files takes many).  The packed
+// chunks each output chunk needs -- the slots of its stored pages and of the owners of its duplicates -- are
+// uploaded just before it, each once, in the order that falls out of that.
 int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const uint32_t* h_ref,
                    const uint32_t* h_crc, uint64_t n_pages, const void* parent_image, uint64_t parent_pages,
                    bool parent_on_device, int verify, uint64_t chunk_pages, grit_restore_stats* stats,
-                   double* h2d_total, double* d2h_total, char* err, size_t errlen, const PeerImages* peers) {
+                   double* h2d_total, double* d2h_total, char* err, size_t errlen, const PeerImages* peers, int lanes,
+                   int depth) {
   GRIT_CUDA(cudaSetDevice(ctx->device));
   if (n_pages > GRIT_MAX_PAGES) return fail(err, errlen, GRIT_EINVAL, "image exceeds GRIT_MAX_PAGES");
   chunk_pages = std::max<uint64_t>(chunk_pages, 256);
@@ -260,23 +264,61 @@ int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const u
   const void* h_packed = io.packed_direct;
   void* h_out = io.out_direct;
   const bool out_pinned = h_out != nullptr, in_pinned = h_packed != nullptr;
+  depth = std::min(std::max(depth, kPipeDepth), kRestoreMaxDepth);
+  if (out_pinned) depth = kPipeDepth;
+  lanes = (int)std::min<uint64_t>(std::max(lanes, 1), std::max<uint64_t>(n_chunks / 4, 1));
+
+  // processing order of the output chunks
+  std::vector<uint64_t> order;
+  order.reserve(n_chunks);
+  {
+    const uint64_t per = (n_chunks + lanes - 1) / std::max(lanes, 1);
+    for (uint64_t k = 0; k < per; k++)
+      for (int l = 0; l < lanes; l++)
+        if (l * per + k < std::min<uint64_t>((l + 1) * per, n_chunks)) order.push_back(l * per + k);
+  }
+  // upload order of the packed chunks, and how far into it each output chunk needs the upload to have come
+  const uint64_t up_chunks = (n_slots + chunk_pages - 1) / chunk_pages;
+  std::vector<uint64_t> up_order, need_upto(n_chunks, 0);
+  {
+    std::vector<char> scheduled(up_chunks, 0);
+    std::vector<uint64_t> want;
+    for (uint64_t i = 0; i < n_chunks; i++) {
+      const uint64_t p0 = order[i] * chunk_pages, p1 = std::min(n_pages, p0 + chunk_pages);
+      want.clear();
+      for (uint64_t p = p0; p < p1; p++) {
+        uint32_t x = h_ref[p];
+        if (GRIT_REF_KIND(x) == GRIT_KIND_DUP && GRIT_REF_VALUE(x) < n_pages) x = h_ref[GRIT_REF_VALUE(x)];
+        if (GRIT_REF_KIND(x) != GRIT_KIND_DATA) continue;
+        const uint64_t c = GRIT_REF_VALUE(x) / chunk_pages;
+        if (c < up_chunks && !scheduled[c]) {
+          scheduled[c] = 1;
+          want.push_back(c);
+        }
+      }
+      std::sort(want.begin(), want.end());
+      up_order.insert(up_order.end(), want.begin(), want.end());
+      need_upto[i] = up_order.size();
+    }
+  }
+  const uint64_t n_up = up_order.size();
 
   struct Res {
-    void *d_packed = nullptr, *d_parent = nullptr, *d_out[kPipeDepth] = {}, *h_stage_out[kPipeDepth] = {};
+    void *d_packed = nullptr, *d_parent = nullptr, *d_out[kRestoreMaxDepth] = {}, *h_stage_out[kRestoreMaxDepth] = {};
     void* h_stage_in[3] = {};
     uint32_t *d_ref = nullptr, *d_crc = nullptr;
-    cudaEvent_t ev_kern[kPipeDepth] = {}, ev_d2h[kPipeDepth] = {};
-    std::vector<cudaEvent_t> ev_up;
+    cudaEvent_t ev_kern[kRestoreMaxDepth] = {}, ev_d2h[kRestoreMaxDepth] = {};
+    cudaEvent_t ev_up = nullptr;  // the latest upload enqueued
     cudaEvent_t ev_stage[3] = {};
     ~Res() {
       cudaDeviceSynchronize();  // nothing of this call may still be running when the cached buffers are reused
-      for (int b = 0; b < kPipeDepth; b++) {
+      for (int b = 0; b < kRestoreMaxDepth; b++) {
         if (ev_kern[b]) cudaEventDestroy(ev_kern[b]);
         if (ev_d2h[b]) cudaEventDestroy(ev_d2h[b]);
       }
       for (int b = 0; b < 3; b++)
         if (ev_stage[b]) cudaEventDestroy(ev_stage[b]);
-      for (auto e : ev_up) cudaEventDestroy(e);
+      if (ev_up) cudaEventDestroy(ev_up);
     }
   } r;
 
@@ -286,12 +328,14 @@ int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const u
   if (int rc = ctx_dev(ctx, kDevRPacked, std::max<uint64_t>(n_slots, 1) * kPage, &r.d_packed, err, errlen)) return rc;
   if (int rc = ctx_dev(ctx, kDevRRef, std::max<uint64_t>(n_pages, 1) * 4, (void**)&r.d_ref, err, errlen)) return rc;
   if (int rc = ctx_dev(ctx, kDevRCrc, std::max<uint64_t>(n_pages, 1) * 4, (void**)&r.d_crc, err, errlen)) return rc;
-  for (int b = 0; b < kPipeDepth; b++) {
-    if (int rc = ctx_dev(ctx, kDevROut0 + b, chunk_bytes, &r.d_out[b], err, errlen)) return rc;
+  GRIT_CUDA(cudaEventCreateWithFlags(&r.ev_up, cudaEventDisableTiming));
+  for (int b = 0; b < depth; b++) {
+    if (int rc = ctx_dev(ctx, b < 3 ? kDevROut0 + b : kDevROutX0 + b - 3, chunk_bytes, &r.d_out[b], err, errlen)) return rc;
     GRIT_CUDA(cudaEventCreateWithFlags(&r.ev_kern[b], cudaEventDisableTiming));
     GRIT_CUDA(cudaEventCreateWithFlags(&r.ev_d2h[b], cudaEventDisableTiming));
     if (!out_pinned)
-      if (int rc = ctx_pin(ctx, kPinRStageOut0 + b, chunk_bytes, &r.h_stage_out[b], err, errlen)) return rc;
+      if (int rc = ctx_pin(ctx, b < 3 ? kPinRStageOut0 + b : kPinRStageOutX0 + b - 3, chunk_bytes, &r.h_stage_out[b], err, errlen))
+        return rc;
   }
   double h2d = 0, d2h = 0;
   if (n_pages) {
@@ -316,20 +360,17 @@ int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const u
   }
   if (int rc = reset_counters(ctx, s, err, errlen)) return rc;
 
-  // upload the packed pages in chunks on the copy stream, one event per chunk
-  const uint64_t up_chunks = (n_slots + chunk_pages - 1) / chunk_pages;
-  r.ev_up.resize(up_chunks, nullptr);
   constexpr int kStageIn = 3;
-  if (!in_pinned && n_slots) {
+  if (!in_pinned && n_up) {
     for (int b = 0; b < kStageIn; b++) {
       if (int rc = ctx_pin(ctx, kPinRStageIn0 + b, chunk_bytes, &r.h_stage_in[b], err, errlen)) return rc;
       GRIT_CUDA(cudaEventCreateWithFlags(&r.ev_stage[b], cudaEventDisableTiming));
     }
   }
 
-  // Callback I/O runs on two helper threads so that reading packed pages, the GPU pipeline and
-  // writing restored pages overlap: the reader keeps the staging-in buffers full ahead of the
-  // upload, the writer drains staging-out buffers as their D2H copies land.
+  // Callback I/O runs on helper threads so that reading packed pages, the GPU pipeline and writing restored pages
+  // overlap: the reader keeps the staging-in buffers full ahead of the upload, the writers drain staging-out
+  // buffers as their D2H copies land.
   struct Helpers {
     std::mutex mu;
     std::condition_variable cv;
@@ -338,12 +379,13 @@ int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const u
       uint64_t p0, p1;
       int b;
     };
-    std::deque<Job> jobs;  // writer
-    uint64_t written = 0;
+    std::deque<Job> jobs;  // writers
+    uint64_t submitted[kRestoreMaxDepth] = {}, finished[kRestoreMaxDepth] = {};  // per staging-out buffer
     int rc = 0;
     bool stop = false;
-    double t_read = 0, t_write = 0, t_write_wait = 0, t_main_wait_read = 0, t_main_wait_write = 0;  // GRITPACK_DEBUG
-    std::thread reader, writer;
+    double t_read = 0, t_write = 0, t_main_wait_read = 0, t_main_wait_write = 0;  // GRITPACK_DEBUG
+    std::thread reader;
+    std::vector<std::thread> writers;
     ~Helpers() {
       {
         std::lock_guard<std::mutex> l(mu);
@@ -351,62 +393,60 @@ int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const u
       }
       cv.notify_all();
       if (reader.joinable()) reader.join();
-      if (writer.joinable()) writer.join();
+      for (auto& w : writers) w.join();
     }
   } hp;
-  if (!in_pinned && up_chunks)
+  if (!in_pinned && n_up)
     hp.reader = std::thread([&] {
       cudaSetDevice(ctx->device);
-      for (uint64_t c = 0; c < up_chunks; c++) {
-        const int b = (int)(c % kStageIn);
-        if (c >= (uint64_t)kStageIn) {  // the slot's previous chunk must have left for the device
+      for (uint64_t k = 0; k < n_up; k++) {
+        const int b = (int)(k % kStageIn);
+        if (k >= (uint64_t)kStageIn) {  // the buffer's previous chunk must have left for the device
           std::unique_lock<std::mutex> l(hp.mu);
-          hp.cv.wait(l, [&] { return hp.stop || hp.consumed > c - kStageIn; });
+          hp.cv.wait(l, [&] { return hp.stop || hp.consumed > k - kStageIn; });
           if (hp.stop) return;
           l.unlock();
           cudaEventSynchronize(r.ev_stage[b]);
         }
-        const uint64_t s0 = c * chunk_pages, n = std::min(chunk_pages, n_slots - s0);
+        const uint64_t s0 = up_order[k] * chunk_pages, n = std::min(chunk_pages, n_slots - s0);
         const double t0 = wall();
         const int rc = io.read_packed(s0, n, r.h_stage_in[b]);
-        hp.t_read += wall() - t0;
         std::lock_guard<std::mutex> l(hp.mu);
+        hp.t_read += wall() - t0;
         if (rc && !hp.rc) hp.rc = rc;
-        hp.filled = c + 1;
+        hp.filled = k + 1;
         hp.cv.notify_all();
         if (rc) return;
       }
     });
   if (!out_pinned && n_chunks)
-    hp.writer = std::thread([&] {
-      cudaSetDevice(ctx->device);
-      for (;;) {
-        Helpers::Job j;
-        {
-          std::unique_lock<std::mutex> l(hp.mu);
-          hp.cv.wait(l, [&] { return hp.stop || !hp.jobs.empty(); });
-          if (hp.jobs.empty()) return;
-          j = hp.jobs.front();
-          hp.jobs.pop_front();
+    for (int w = 0; w < std::min(depth - 1, 4); w++)
+      hp.writers.emplace_back([&] {
+        cudaSetDevice(ctx->device);
+        for (;;) {
+          Helpers::Job j;
+          {
+            std::unique_lock<std::mutex> l(hp.mu);
+            hp.cv.wait(l, [&] { return hp.stop || !hp.jobs.empty(); });
+            if (hp.jobs.empty()) return;
+            j = hp.jobs.front();
+            hp.jobs.pop_front();
+          }
+          int rc = cudaEventSynchronize(r.ev_d2h[j.b]) == cudaSuccess ? 0 : GRIT_ECUDA;
+          const double t1 = wall();
+          if (!rc) rc = io.write_out(j.p0, j.p1, r.h_stage_out[j.b]);
+          std::lock_guard<std::mutex> l(hp.mu);
+          hp.t_write += wall() - t1;
+          if (rc && !hp.rc) hp.rc = rc;
+          hp.finished[j.b]++;
+          hp.cv.notify_all();
         }
-        const double t0 = wall();
-        int rc = cudaEventSynchronize(r.ev_d2h[j.b]) == cudaSuccess ? 0 : GRIT_ECUDA;
-        const double t1 = wall();
-        if (!rc) rc = io.write_out(j.p0, j.p1, r.h_stage_out[j.b]);
-        hp.t_write_wait += t1 - t0;
-        hp.t_write += wall() - t1;
-        std::lock_guard<std::mutex> l(hp.mu);
-        if (rc && !hp.rc) hp.rc = rc;
-        hp.written++;
-        hp.cv.notify_all();
-      }
-    });
+      });
 
-  uint64_t uploaded = 0;  // upload chunks enqueued so far
-  auto upload_until = [&](uint64_t slot_end) -> int {
-    const uint64_t need = std::min(up_chunks, (slot_end + chunk_pages - 1) / chunk_pages);
-    for (; uploaded < need; uploaded++) {
-      const uint64_t s0 = uploaded * chunk_pages, n = std::min(chunk_pages, n_slots - s0);
+  uint64_t uploaded = 0;  // positions of up_order enqueued so far
+  auto upload_upto = [&](uint64_t pos) -> int {
+    for (; uploaded < pos; uploaded++) {
+      const uint64_t s0 = up_order[uploaded] * chunk_pages, n = std::min(chunk_pages, n_slots - s0);
       const char* src = static_cast<const char*>(h_packed) + s0 * kPage;
       const int b = (int)(uploaded % kStageIn);
       if (!in_pinned) {  // no pinned source: the reader thread fills pinned staging
@@ -424,8 +464,6 @@ int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const u
         hp.consumed = uploaded + 1;
         hp.cv.notify_all();
       }
-      GRIT_CUDA(cudaEventCreateWithFlags(&r.ev_up[uploaded], cudaEventDisableTiming));
-      GRIT_CUDA(cudaEventRecord(r.ev_up[uploaded], ctx->h2d));
       h2d += (double)n * kPage;
     }
     return GRIT_OK;
@@ -433,15 +471,15 @@ int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const u
 
   GRIT_CUDA(cudaEventRecord(ctx->ev0, s));
   const double t_loop = wall();
-  uint64_t slot_front = 0;  // slots referenced by pages before the current chunk end
   for (uint64_t i = 0; i < n_chunks; i++) {
-    const int b = (int)(i % kPipeDepth);
-    const uint64_t p0 = i * chunk_pages, p1 = std::min(n_pages, p0 + chunk_pages);
-    for (uint64_t p = p0; p < p1; p++)
-      if (GRIT_REF_KIND(h_ref[p]) == GRIT_KIND_DATA) slot_front = std::max<uint64_t>(slot_front, GRIT_REF_VALUE(h_ref[p]) + 1);
-    if (int rc = upload_until(std::min(slot_front, n_slots))) return rc;
-    if (uploaded) GRIT_CUDA(cudaStreamWaitEvent(s, r.ev_up[uploaded - 1], 0));
-    if (i >= (uint64_t)kPipeDepth) GRIT_CUDA(cudaStreamWaitEvent(s, r.ev_d2h[b], 0));
+    const int b = (int)(i % depth);
+    const uint64_t p0 = order[i] * chunk_pages, p1 = std::min(n_pages, p0 + chunk_pages);
+    if (uploaded < need_upto[i]) {
+      if (int rc = upload_upto(need_upto[i])) return rc;
+      GRIT_CUDA(cudaEventRecord(r.ev_up, ctx->h2d));  // one copy stream: the latest upload covers all before it
+    }
+    if (uploaded) GRIT_CUDA(cudaStreamWaitEvent(s, r.ev_up, 0));
+    if (i >= (uint64_t)depth) GRIT_CUDA(cudaStreamWaitEvent(s, r.ev_d2h[b], 0));
     GRIT_CUDA(launch_restore(ctx->geom, ctx->d_tables, r.d_packed, n_slots, r.d_ref, r.d_crc, n_pages, p0, p1, imgs,
                              r.d_out[b], verify, ctx->d_cnt, s));
     ctx->launches++;
@@ -449,10 +487,10 @@ int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const u
     GRIT_CUDA(cudaStreamWaitEvent(ctx->d2h, r.ev_kern[b], 0));
     char* dst = static_cast<char*>(h_out) + p0 * kPage;
     if (!out_pinned) {
-      if (i >= (uint64_t)kPipeDepth) {  // staging buffer b still holds chunk i - depth until the writer is done with it
+      {  // staging buffer b still holds an earlier chunk until a writer is done with it
         const double t0 = wall();
         std::unique_lock<std::mutex> l(hp.mu);
-        hp.cv.wait(l, [&] { return hp.rc || hp.written > i - kPipeDepth; });
+        hp.cv.wait(l, [&] { return hp.rc || hp.finished[b] == hp.submitted[b]; });
         hp.t_main_wait_write += wall() - t0;
         if (hp.rc) return fail(err, errlen, hp.rc, "writing restored pages failed");
       }
@@ -463,27 +501,32 @@ int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const u
     d2h += (double)(p1 - p0) * kPage;
     if (!out_pinned) {
       std::lock_guard<std::mutex> l(hp.mu);
+      hp.submitted[b]++;
       hp.jobs.push_back({p0, p1, b});
       hp.cv.notify_all();
     }
   }
-  if (int rc = upload_until(n_slots)) return rc;  // nothing may be left half-sent
   GRIT_CUDA(cudaEventRecord(ctx->ev1, s));
   if (int rc = read_counters(ctx, s, err, errlen)) return rc;
   GRIT_CUDA(cudaStreamSynchronize(ctx->d2h));
   GRIT_CUDA(cudaStreamSynchronize(ctx->h2d));
-  if (!out_pinned) {  // the writer finishes the tail
+  if (!out_pinned) {  // the writers finish the tail
     std::unique_lock<std::mutex> l(hp.mu);
-    hp.cv.wait(l, [&] { return hp.rc || hp.written == n_chunks; });
+    hp.cv.wait(l, [&] {
+      if (hp.rc) return true;
+      for (int b = 0; b < depth; b++)
+        if (hp.finished[b] != hp.submitted[b]) return false;
+      return true;
+    });
     if (hp.rc) return fail(err, errlen, hp.rc, "writing restored pages failed");
   }
   if (h2d_total) *h2d_total += h2d;
   if (d2h_total) *d2h_total += d2h;
   if (debug_on())
     fprintf(stderr,
-            "[gritpack] restore_stream: alloc %.1f ms, stream %.1f ms (reader busy %.1f, writer busy %.1f + %.1f waiting for "
-            "the D2H, main thread waited %.1f for the reader and %.1f for the writer)\n",
-            (t_loop - t_begin) * 1e3, (wall() - t_loop) * 1e3, hp.t_read * 1e3, hp.t_write * 1e3, hp.t_write_wait * 1e3,
+            "[gritpack] restore_stream: alloc %.1f ms, stream %.1f ms (%d lanes, depth %d; reader busy %.1f, writers busy %.1f "
+            "in all, main thread waited %.1f for the reader and %.1f for the writers)\n",
+            (t_loop - t_begin) * 1e3, (wall() - t_loop) * 1e3, lanes, depth, hp.t_read * 1e3, hp.t_write * 1e3,
             hp.t_main_wait_read * 1e3, hp.t_main_wait_write * 1e3);
   const DevCounters& c = *ctx->h_cnt;
   if (stats) {

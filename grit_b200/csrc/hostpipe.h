@@ -16,6 +16,7 @@
 namespace grit {
 
 constexpr int kPipeDepth = 3;  // chunks in flight
+constexpr int kRestoreMaxDepth = 8;  // output chunks in flight of a restore that writes through callbacks
 
 // Packs a stream of page chunks.  Call order: begin, then for each chunk
 // submit(i) ... collect(i) (collect may lag submit by up to kPipeDepth-1), finish.
@@ -85,7 +86,8 @@ struct RestoreIO {
   const void* packed_direct = nullptr;
   std::function<int(uint64_t slot0, uint64_t n_slots, void* dst_pinned)> read_packed;
   void* out_direct = nullptr;
-  // called in page order, on the calling thread, once the chunk has landed in host memory
+  // called once per output chunk, from writer threads (several at a time, any order), when the chunk has landed in
+  // host memory
   std::function<int(uint64_t page0, uint64_t page1, const void* src_pinned)> write_out;
 };
 
@@ -95,7 +97,8 @@ struct RestoreIO {
 int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const uint32_t* h_ref,
                    const uint32_t* h_crc, uint64_t n_pages, const void* parent_image, uint64_t parent_pages,
                    bool parent_on_device, int verify, uint64_t chunk_pages, grit_restore_stats* stats,
-                   double* h2d_bytes, double* d2h_bytes, char* err, size_t errlen, const PeerImages* peers = nullptr);
+                   double* h2d_bytes, double* d2h_bytes, char* err, size_t errlen, const PeerImages* peers = nullptr,
+                   int lanes = 1, int depth = kPipeDepth);
 
 bool is_pinned(const void* p);
 

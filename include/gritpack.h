@@ -116,6 +116,15 @@ uint32_t grit_crc32c(uint32_t crc, const void *data, size_t len);
 int grit_ctx_create(int device, grit_ctx **out, char *err, size_t errlen);
 void grit_ctx_destroy(grit_ctx *ctx);
 
+/* Brings the CUDA runtime up on `device` (primary context, this library's device
+ * code) and returns; safe to call from any thread, any number of times.  A
+ * process's first CUDA call costs 0.3-0.5 s on a B200 box whatever it does: an
+ * agent calls this on a thread of its own at start-up -- before
+ * RuntimeCheckpointPod on upload (checkpoint.go:14), so that the cost hides behind
+ * the CRIU dump -- and the directory calls find the device ready.  The reference
+ * has no such start-up cost and no counterpart. */
+int grit_warmup(int device);
+
 /* Number of kernels this context has launched (bench.py's gpu_launches). */
 uint64_t grit_ctx_launches(const grit_ctx *ctx);
 
