@@ -89,6 +89,8 @@ SYMBOLS = {
     "grit_synth_image": (_I, [_P, _P, _U64, _U64, _U64, _U32, _U32, _U32, _P] + _ERR),
     "grit_pack_host": (_I, [_P, _P, _U64, C.POINTER(Table), _P, _U64, _P, _P, _P, C.POINTER(PackStats)] + _ERR),
     "grit_restore_host": (_I, [_P, _P, _U64, _P, _P, _U64, _P, _U64, _P, _I, C.POINTER(RestoreStats)] + _ERR),
+    "grit_restore_to_device": (_I, [_P, _P, _P, _P, _U64, _P, _P, _U64, _P, _U64, C.POINTER(_P), C.POINTER(_U64), _U32, _P,
+                                    _I, _U64, C.POINTER(RestoreStats)] + _ERR),
     "grit_pin_host": (_I, [_P, C.c_size_t]),
     "grit_unpin_host": (_I, [_P]),
     "grit_pack_dir": (_I, [C.c_char_p, C.c_char_p, C.POINTER(Opts), C.POINTER(Stats)] + _ERR),
@@ -97,6 +99,8 @@ SYMBOLS = {
     "grit_image_deps": (_I, [C.c_char_p, C.c_int, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t)] + _ERR),
     "grit_write_sentinel": (_I, [C.c_char_p, C.c_char_p]),
 }
+
+READ_PACKED_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p)
 
 _lib = None
 

@@ -180,6 +180,26 @@ class Context:
         return out, st.as_dict()
 
 
+    def restore_to_device(self, packed, ref, crc, out, parent_image=None, peer_images=(), verify=True, chunk_bytes=0,
+                          read=None, n_slots=None, check=True):
+        """grit_restore_to_device: packed (CPU tensor, or None with `read(slot0, n, dst_ptr) -> int`) streams through a
+        device ring into `out` (CUDA tensor of the whole image); ref / crc are CPU tensors."""
+        n = ref.numel()
+        npeer = len(peer_images)
+        imgs = (C.c_void_p * max(npeer, 1))(*[(i.data_ptr() if i is not None else None) for i in peer_images])
+        cnts = (C.c_uint64 * max(npeer, 1))(*[(i.numel() // PAGE if i is not None else 0) for i in peer_images])
+        cb = _lib.READ_PACKED_FN(lambda user, s0, k, dst: int(read(s0, k, dst))) if read is not None else None
+        slots = n_slots if n_slots is not None else packed.numel() // PAGE
+        st, err = RestoreStats(), _lib.errbuf()
+        rc = self.lib.grit_restore_to_device(
+            self.handle, _ptr(packed), C.cast(cb, C.c_void_p) if cb else None, None, slots, _ptr(ref), _ptr(crc), n,
+            _ptr(parent_image), parent_image.numel() // PAGE if parent_image is not None else 0, imgs, cnts, npeer,
+            _ptr(out), int(verify), chunk_bytes, C.byref(st), err, len(err))
+        if check:
+            _lib.check(rc, err)
+        return out, st.as_dict()
+
+
 def crc32c(data, crc=0):
     """Host CRC-32C (Go: crc32.Update with the Castagnoli table)."""
     b = bytes(data)

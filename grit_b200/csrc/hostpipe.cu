@@ -543,9 +543,201 @@ int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const u
   return GRIT_OK;
 }
 
+
+// ------------------------------------------------------------------ restore into HBM, packed input through a ring
+// BASELINE configs[4]: the destination -- the whole image, up to all of HBM -- is the one big allocation; the packed
+// pages never are.  They arrive chunk by chunk in a small device ring; slots are numbered in page order, so packed
+// chunk c serves a run of consecutive pages [first page whose slot is in c, first page whose slot is in c + 1), and
+// one K4 launch restores that run straight into its place in d_out.  A duplicate of a page restored by an earlier
+// launch is copied from d_out (its owner's slot may have left the ring); parent / peer pages come from their
+// images as always.  Device memory beside d_out: ring (4 chunks) + 8 bytes per page.
+int restore_to_device(grit_ctx* ctx, const void* h_packed, const std::function<int(uint64_t, uint64_t, void*)>& read_packed,
+                      uint64_t n_slots, const uint32_t* h_ref, const uint32_t* h_crc, uint64_t n_pages,
+                      const void* d_parent, uint64_t parent_pages, const PeerImages* peers, void* d_out, int verify,
+                      uint64_t chunk_pages, grit_restore_stats* stats, double* h2d_total, char* err, size_t errlen) {
+  GRIT_CUDA(cudaSetDevice(ctx->device));
+  if (n_pages > GRIT_MAX_PAGES) return fail(err, errlen, GRIT_EINVAL, "image exceeds GRIT_MAX_PAGES");
+  chunk_pages = std::max<uint64_t>(chunk_pages, 256);
+  constexpr int kRing = 4, kStage = 3;
+  const bool in_pinned = h_packed && is_pinned(h_packed);
+  const uint64_t up_chunks = (n_slots + chunk_pages - 1) / chunk_pages;
+  // run of pages each packed chunk serves: page_end[c] = first page whose stored slot lies beyond chunk c
+  std::vector<uint64_t> page_end(std::max<uint64_t>(up_chunks, 1), n_pages);
+  {
+    uint64_t c = 0;
+    for (uint64_t p = 0; p < n_pages && up_chunks; p++)
+      if (GRIT_REF_KIND(h_ref[p]) == GRIT_KIND_DATA) {
+        const uint64_t pc = GRIT_REF_VALUE(h_ref[p]) / chunk_pages;
+        if (pc < c || pc >= up_chunks)
+          return fail(err, errlen, GRIT_ECRC, "restore: page %llu stores slot %u out of order; the image cannot be streamed",
+                      (unsigned long long)p, GRIT_REF_VALUE(h_ref[p]));
+        while (c < pc) page_end[c++] = p;
+      }
+  }
+  struct Res {
+    cudaEvent_t ev_up[kRing] = {}, ev_kern[kRing] = {}, ev_stage[kStage] = {};
+    ~Res() {
+      cudaDeviceSynchronize();
+      for (auto e : ev_up)
+        if (e) cudaEventDestroy(e);
+      for (auto e : ev_kern)
+        if (e) cudaEventDestroy(e);
+      for (auto e : ev_stage)
+        if (e) cudaEventDestroy(e);
+    }
+  } r;
+  void *d_ring[kRing] = {}, *h_stage[kStage] = {};
+  uint32_t *d_ref = nullptr, *d_crc = nullptr;
+  const size_t chunk_bytes = chunk_pages * kPage;
+  for (int b = 0; b < kRing; b++) {
+    if (int rc = ctx_dev(ctx, b < 3 ? kDevROut0 + b : kDevROutX0, chunk_bytes, &d_ring[b], err, errlen)) return rc;
+    GRIT_CUDA(cudaEventCreateWithFlags(&r.ev_up[b], cudaEventDisableTiming));
+    GRIT_CUDA(cudaEventCreateWithFlags(&r.ev_kern[b], cudaEventDisableTiming));
+  }
+  if (int rc = ctx_dev(ctx, kDevRRef, std::max<uint64_t>(n_pages, 1) * 4, (void**)&d_ref, err, errlen)) return rc;
+  if (int rc = ctx_dev(ctx, kDevRCrc, std::max<uint64_t>(n_pages, 1) * 4, (void**)&d_crc, err, errlen)) return rc;
+  if (!in_pinned && up_chunks)
+    for (int b = 0; b < kStage; b++) {
+      if (int rc = ctx_pin(ctx, kPinRStageIn0 + b, chunk_bytes, &h_stage[b], err, errlen)) return rc;
+      GRIT_CUDA(cudaEventCreateWithFlags(&r.ev_stage[b], cudaEventDisableTiming));
+    }
+  cudaStream_t s = ctx->stream;
+  double h2d = 0;
+  if (n_pages) {
+    GRIT_CUDA(cudaMemcpyAsync(d_ref, h_ref, n_pages * 4, cudaMemcpyHostToDevice, s));
+    if (h_crc) GRIT_CUDA(cudaMemcpyAsync(d_crc, h_crc, n_pages * 4, cudaMemcpyHostToDevice, s));
+    h2d += n_pages * 8.0;
+  }
+  PeerImages imgs{};
+  if (peers) imgs = *peers;
+  imgs.parent = static_cast<const unsigned char*>(d_parent);
+  imgs.parent_pages = d_parent ? parent_pages : 0;
+  if (int rc = reset_counters(ctx, s, err, errlen)) return rc;
+
+  // without a pinned source a reader thread keeps pinned staging full ahead of the upload
+  struct Reader {
+    std::mutex mu;
+    std::condition_variable cv;
+    uint64_t filled = 0, consumed = 0;
+    int rc = 0;
+    bool stop = false;
+    std::thread th;
+    ~Reader() {
+      {
+        std::lock_guard<std::mutex> l(mu);
+        stop = true;
+      }
+      cv.notify_all();
+      if (th.joinable()) th.join();
+    }
+  } rd;
+  if (!in_pinned && up_chunks)
+    rd.th = std::thread([&] {
+      cudaSetDevice(ctx->device);
+      for (uint64_t c = 0; c < up_chunks; c++) {
+        const int b = (int)(c % kStage);
+        if (c >= (uint64_t)kStage) {
+          std::unique_lock<std::mutex> l(rd.mu);
+          rd.cv.wait(l, [&] { return rd.stop || rd.consumed > c - kStage; });
+          if (rd.stop) return;
+          l.unlock();
+          cudaEventSynchronize(r.ev_stage[b]);
+        }
+        const uint64_t s0 = c * chunk_pages, n = std::min(chunk_pages, n_slots - s0);
+        int rc = 0;
+        if (read_packed) rc = read_packed(s0, n, h_stage[b]);
+        else memcpy(h_stage[b], static_cast<const char*>(h_packed) + s0 * kPage, n * kPage);
+        std::lock_guard<std::mutex> l(rd.mu);
+        if (rc && !rd.rc) rd.rc = rc;
+        rd.filled = c + 1;
+        rd.cv.notify_all();
+        if (rc) return;
+      }
+    });
+
+  GRIT_CUDA(cudaEventRecord(ctx->ev0, s));
+  uint64_t page0 = 0;
+  for (uint64_t c = 0; c < std::max<uint64_t>(up_chunks, 1); c++) {
+    const int b = (int)(c % kRing);
+    uint64_t n = 0;
+    if (up_chunks) {
+      const uint64_t s0 = c * chunk_pages;
+      n = std::min(chunk_pages, n_slots - s0);
+      const char* src = static_cast<const char*>(h_packed) + s0 * kPage;
+      if (!in_pinned) {
+        std::unique_lock<std::mutex> l(rd.mu);
+        rd.cv.wait(l, [&] { return rd.rc || rd.filled > c; });
+        if (rd.rc) return fail(err, errlen, rd.rc, "reading packed pages failed");
+        src = static_cast<const char*>(h_stage[c % kStage]);
+      }
+      if (c >= (uint64_t)kRing) GRIT_CUDA(cudaStreamWaitEvent(ctx->h2d, r.ev_kern[b], 0));  // ring slot still being read
+      GRIT_CUDA(cudaMemcpyAsync(d_ring[b], src, n * kPage, cudaMemcpyHostToDevice, ctx->h2d));
+      GRIT_CUDA(cudaEventRecord(r.ev_up[b], ctx->h2d));
+      if (!in_pinned) {
+        GRIT_CUDA(cudaEventRecord(r.ev_stage[c % kStage], ctx->h2d));
+        std::lock_guard<std::mutex> l(rd.mu);
+        rd.consumed = c + 1;
+        rd.cv.notify_all();
+      }
+      h2d += (double)n * kPage;
+      GRIT_CUDA(cudaStreamWaitEvent(s, r.ev_up[b], 0));
+    }
+    const uint64_t page1 = page_end[c];
+    PackedWindow win;
+    win.slot0 = c * chunk_pages;
+    win.restored = static_cast<const uint4*>(d_out);
+    GRIT_CUDA(launch_restore(ctx->geom, ctx->d_tables, d_ring[b], n, d_ref, d_crc, n_pages, page0, page1, imgs,
+                             static_cast<char*>(d_out) + page0 * kPage, verify, ctx->d_cnt, s, win));
+    ctx->launches++;
+    GRIT_CUDA(cudaEventRecord(r.ev_kern[b], s));
+    page0 = page1;
+  }
+  GRIT_CUDA(cudaEventRecord(ctx->ev1, s));
+  if (int rc = read_counters(ctx, s, err, errlen)) return rc;
+  GRIT_CUDA(cudaStreamSynchronize(ctx->h2d));
+  if (h2d_total) *h2d_total += h2d;
+  const DevCounters& k = *ctx->h_cnt;
+  if (stats) {
+    stats->n_pages = n_pages;
+    stats->n_bad = k.n_bad;
+    stats->first_bad = k.first_bad;
+    float ms = 0;
+    cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+    stats->gpu_ms = ms;
+  }
+  if (k.n_bad)
+    return fail(err, errlen, GRIT_ECRC, "restore: %llu page(s) failed CRC-32C or had a bad reference, first page %llu",
+                (unsigned long long)k.n_bad, (unsigned long long)k.first_bad);
+  return GRIT_OK;
+}
+
 }  // namespace grit
 
 extern "C" {
+
+int grit_restore_to_device(grit_ctx* ctx, const void* h_packed, grit_read_packed_fn read, void* user, uint64_t n_slots,
+                           const uint32_t* h_ref, const uint32_t* h_crc, uint64_t n_pages, const void* d_parent_image,
+                           uint64_t parent_pages, const void* const* d_peer_images, const uint64_t* peer_pages,
+                           uint32_t n_peers, void* d_out, int verify, uint64_t chunk_bytes, grit_restore_stats* stats,
+                           char* err, size_t errlen) {
+  if (!ctx) return fail(err, errlen, GRIT_EINVAL, "null context");
+  if (n_peers > GRIT_MAX_PEERS) return fail(err, errlen, GRIT_EINVAL, "n_peers %u > %u", n_peers, GRIT_MAX_PEERS);
+  if (n_pages && (!h_ref || !d_out || (verify && !h_crc) || (n_slots && !h_packed && !read)))
+    return fail(err, errlen, GRIT_EINVAL, "null buffer");
+  if (reinterpret_cast<uintptr_t>(d_out) & 15) return fail(err, errlen, GRIT_EINVAL, "buffer is not 16-byte aligned");
+  PeerImages imgs{};
+  imgs.n_peers = n_peers;
+  for (uint32_t r = 0; r < n_peers; r++) {
+    imgs.peer[r] = static_cast<const unsigned char*>(d_peer_images ? d_peer_images[r] : nullptr);
+    imgs.peer_pages[r] = (imgs.peer[r] && peer_pages) ? peer_pages[r] : 0;
+  }
+  std::function<int(uint64_t, uint64_t, void*)> cb;
+  if (read) cb = [read, user](uint64_t s0, uint64_t n, void* dst) { return read(user, s0, n, dst); };
+  std::lock_guard<std::mutex> g(ctx->mu);
+  const uint64_t chunk_pages = chunk_bytes >= (1u << 20) ? chunk_bytes / kPage : host_chunk_pages();
+  return restore_to_device(ctx, read ? nullptr : h_packed, cb, n_slots, h_ref, h_crc, n_pages, d_parent_image, parent_pages,
+                           &imgs, d_out, verify, chunk_pages, stats, nullptr, err, errlen);
+}
 
 int grit_pin_host(void* h_ptr, size_t bytes) {
   return cudaHostRegister(h_ptr, bytes, cudaHostRegisterDefault) == cudaSuccess ? GRIT_OK : GRIT_ECUDA;

@@ -100,6 +100,12 @@ int restore_stream(grit_ctx* ctx, const RestoreIO& io, uint64_t n_slots, const u
                    double* h2d_bytes, double* d2h_bytes, char* err, size_t errlen, const PeerImages* peers = nullptr,
                    int lanes = 1, int depth = kPipeDepth);
 
+// restore into a device buffer with the packed pages streaming through a small device ring (configs[4])
+int restore_to_device(grit_ctx* ctx, const void* h_packed, const std::function<int(uint64_t, uint64_t, void*)>& read_packed,
+                      uint64_t n_slots, const uint32_t* h_ref, const uint32_t* h_crc, uint64_t n_pages,
+                      const void* d_parent, uint64_t parent_pages, const PeerImages* peers, void* d_out, int verify,
+                      uint64_t chunk_pages, grit_restore_stats* stats, double* h2d_total, char* err, size_t errlen);
+
 bool is_pinned(const void* p);
 
 }  // namespace grit

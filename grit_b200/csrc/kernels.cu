@@ -926,18 +926,23 @@ struct PageSrc {
 
 __device__ __forceinline__ PageSrc resolve_source(uint64_t p, bool on, const uint4* __restrict__ packed,
                                                   uint64_t n_slots, const uint32_t* __restrict__ ref,
-                                                  uint64_t n_pages, const PeerImages& imgs) {
+                                                  uint64_t n_pages, const PeerImages& imgs, const PackedWindow& win,
+                                                  uint64_t page0) {
   PageSrc r{nullptr, false};
   if (!on) return r;
   uint32_t x = ref[p], kind = x >> 29, v = x & 0x1FFFFFFFu;
-  if (kind == 2u) {  // DUP -> the owner's slot
+  if (kind == 2u) {  // DUP -> the owner's slot, or (windowed restore) the owner's page where an earlier launch put it
     const uint32_t x2 = v < n_pages ? ref[v] : 0u;
     r.bad = (x2 >> 29) != 1u;
+    if (win.restored && v < page0) {
+      if (!r.bad) r.src = win.restored + (uint64_t)v * 256;
+      return r;
+    }
     kind = 1u;
     v = x2 & 0x1FFFFFFFu;
   }
-  if (kind == 1u) {
-    if (!r.bad && v < n_slots) r.src = packed + (uint64_t)v * 256;
+  if (kind == 1u) {  // `packed` holds slots [win.slot0, win.slot0 + n_slots)
+    if (!r.bad && v >= win.slot0 && v - win.slot0 < n_slots) r.src = packed + (uint64_t)(v - win.slot0) * 256;
     else r.bad = true;
   } else if (kind == 3u) {
     if (imgs.parent && v < imgs.parent_pages) r.src = reinterpret_cast<const uint4*>(imgs.parent) + (uint64_t)v * 256;
@@ -957,7 +962,7 @@ __device__ __forceinline__ PageSrc resolve_source(uint64_t p, bool on, const uin
 __global__ void __launch_bounds__(kThreads, 1)
 k_restore(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ packed, uint64_t n_slots,
           const uint32_t* __restrict__ ref, const uint32_t* __restrict__ crc, uint64_t n_pages,
-          uint64_t page0, uint64_t page1, PeerImages imgs, uint4* __restrict__ out, int verify,
+          uint64_t page0, uint64_t page1, PeerImages imgs, PackedWindow win, uint4* __restrict__ out, int verify,
           DevCounters* __restrict__ cnt) {
   if (verify) load_tables(tabs);
   const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -970,7 +975,7 @@ k_restore(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ packed, 
   for (; grp < n_groups; grp += stride) {
     const uint64_t p = page0 + 4 * grp + g;
     const bool on = p < page1;
-    const PageSrc ps = resolve_source(p, on, packed, n_slots, ref, n_pages, imgs);
+    const PageSrc ps = resolve_source(p, on, packed, n_slots, ref, n_pages, imgs, win, page0);
     const bool have = ps.src != nullptr;
     bool bad = ps.bad;
     const uint4* s = have ? ps.src + l : packed;  // never dereferenced without a source
@@ -1143,11 +1148,11 @@ cudaError_t launch_compact(const LaunchGeom& g, const void* d_image, uint64_t n_
 cudaError_t launch_restore(const LaunchGeom& g, const Gf2Tables* d_tab, const void* d_packed, uint64_t n_slots,
                            const uint32_t* d_ref, const uint32_t* d_crc, uint64_t n_pages, uint64_t page0,
                            uint64_t page1, PeerImages imgs, void* d_out, int verify, DevCounters* d_cnt,
-                           cudaStream_t s) {
+                           cudaStream_t s, PackedWindow win) {
   if (page1 <= page0) return cudaSuccess;
   const int grid = grid_for(g, (page1 - page0 + 3) / 4, kWarps, 1);
   k_restore<<<grid, kThreads, verify ? kSmBytes : 0, s>>>(d_tab, static_cast<const uint4*>(d_packed), n_slots,
-                                                          d_ref, d_crc, n_pages, page0, page1, imgs,
+                                                          d_ref, d_crc, n_pages, page0, page1, imgs, win,
                                                           static_cast<uint4*>(d_out), verify, d_cnt);
   return cudaGetLastError();
 }

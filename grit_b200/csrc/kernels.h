@@ -55,6 +55,15 @@ struct PeerImages {
   uint32_t n_peers;
 };
 
+// K4 with only part of the packed image on the device (a restore whose packed input streams through a ring):
+// the packed pointer holds slots [slot0, slot0 + n_slots); a duplicate whose owner page lies in front of the launch's
+// first page is copied from the restored image itself (`restored`, the whole image on the device) instead of from
+// the owner's slot, which may have left the ring.  {0, nullptr}: the whole packed image is there.
+struct PackedWindow {
+  uint64_t slot0 = 0;
+  const uint4* restored = nullptr;
+};
+
 // counters written by the kernels, read back by the host after a sync
 struct DevCounters {
   unsigned long long kind[5];    // pages per GRIT_KIND_*, filled by compact
@@ -108,7 +117,7 @@ uint32_t fused_tile_pages();
 cudaError_t launch_restore(const LaunchGeom& g, const Gf2Tables* d_tab, const void* d_packed,
                            uint64_t n_slots, const uint32_t* d_ref, const uint32_t* d_crc,
                            uint64_t n_pages, uint64_t page0, uint64_t page1, PeerImages imgs, void* d_out,
-                           int verify, DevCounters* d_cnt, cudaStream_t s);
+                           int verify, DevCounters* d_cnt, cudaStream_t s, PackedWindow win = PackedWindow{});
 cudaError_t launch_synth(const LaunchGeom& g, void* d_image, uint64_t n_pages, uint64_t page_base,
                          uint64_t seed, uint32_t pct_zero, uint32_t pct_dup, uint32_t dup_pool,
                          cudaStream_t s);

@@ -308,6 +308,30 @@ int grit_restore_host(grit_ctx *ctx, const void *h_packed, uint64_t n_slots,
                       uint64_t n_pages, const void *h_parent_image,
                       uint64_t parent_pages, void *h_out, int verify,
                       grit_restore_stats *stats, char *err, size_t errlen);
+/* Restore straight into a device buffer, for images that fill the GPU (BASELINE
+ * configs[4]: download + CRC verify + reassembly of a full-HBM image).  d_out,
+ * n_pages * 4096 bytes, is the only large device allocation: the packed pages
+ * are taken from host memory (h_packed: the whole packed image, pinned for full
+ * PCIe rate) or from `read` (called from a helper thread, in slot order, to fill
+ * a pinned staging buffer with slots [slot0, slot0 + n_slots); non-zero return
+ * aborts) and pass through a ring of four chunks on the device (chunk_bytes
+ * each, 0 = 64 MiB).  Slots must be numbered in page order, as every pack of
+ * this library numbers them.  The restore of a duplicate copies its owner's page
+ * from d_out.  h_ref / h_crc are host arrays; the parent and peer images are
+ * DEVICE pointers as in grit_restore_buffer.  What copyFile's destination is to
+ * the reference (copy.go:73-79) d_out is here: the consumer's memory itself,
+ * with no file in between. */
+typedef int (*grit_read_packed_fn)(void *user, uint64_t slot0, uint64_t n_slots,
+                                   void *dst_pinned);
+int grit_restore_to_device(grit_ctx *ctx, const void *h_packed,
+                           grit_read_packed_fn read, void *user,
+                           uint64_t n_slots, const uint32_t *h_ref,
+                           const uint32_t *h_crc, uint64_t n_pages,
+                           const void *d_parent_image, uint64_t parent_pages,
+                           const void *const *d_peer_images,
+                           const uint64_t *peer_pages, uint32_t n_peers,
+                           void *d_out, int verify, uint64_t chunk_bytes,
+                           grit_restore_stats *stats, char *err, size_t errlen);
 /* cudaHostRegister / Unregister of a caller buffer, so that the two calls
  * above copy at full PCIe rate. */
 int grit_pin_host(void *h_ptr, size_t bytes);
