@@ -727,6 +727,12 @@ def run_gritpack(args):
     if rank == 0 and world == 1 and not args.no_dir:
         e2e_dir = measure_e2e_dir(torch, ctx, image, n_pages)
 
+    # ---- configs[4]: full-HBM restore stress (every rank, sized to what the GPU and the host can hold)
+    stress = None
+    if not args.no_stress:
+        image = packed = restored = meta = r = rr = peer_images = full = parent_tab = hr = None   # frees HBM and pinned memory
+        stress = restore_stress(torch, dist, ctx, rank, world, e2e["link"]["h2d_gbs"] if e2e else None)
+
     # ---- CPU baseline on this box's host cores (rank 0, N=1 only): bounded samples
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -755,6 +761,7 @@ def run_gritpack(args):
             "pack_gbs": round(world * n_bytes / (t_pack * 1e-3) / 1e9, 1),
             "restore_gbs": round(world * n_bytes / (t_restore * 1e-3) / 1e9, 1),
             "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "e2e_dir": e2e_dir, "other_mixes": other,
+            "restore_stress": stress,
             "gpu_launches": int(launches),
             "clocks": clocks, "bit_exact": True,
         }
@@ -764,6 +771,79 @@ def run_gritpack(args):
     if world > 1:
         dist.destroy_process_group()
     return 0
+
+
+# ----------------------------------------------------------------------------- configs[4]: full-HBM restore stress
+def restore_stress(torch, dist, ctx, rank, world, link_h2d):
+    """The largest C1-mix image this GPU (and this box's host memory) can take is restored into HBM with the packed
+    pages streaming from pinned host memory through grit_restore_to_device's four-chunk device ring: download + CRC
+    verify + reassembly, the destination being the only large device allocation.  The packed image is made piece by
+    piece beforehand (synthesise 2 GiB in place, K1 + K2 + K3, D2H); duplicates are found within a piece."""
+    import ctypes as C
+    import psutil
+    from grit_b200 import _lib
+    dev = torch.device("cuda", ctx.device)
+    torch.cuda.empty_cache()
+    free, _ = torch.cuda.mem_get_info()
+    avail = psutil.virtual_memory().available
+    piece = (2 * GiB) // PAGE
+    n_pages = min(int(180e9) // PAGE, (free - 8 * GiB) // PAGE, int(avail * 0.55 / max(world, 1) / 0.78) // PAGE, (1 << 26) - 1)
+    n_pages = n_pages // piece * piece
+    if n_pages < piece:
+        return {"skipped": f"free HBM {free >> 30} GiB, host memory {avail >> 30} GiB"}
+    out = torch.empty(n_pages * PAGE, dtype=torch.uint8, device=dev)
+    tmp = torch.empty(piece * PAGE, dtype=torch.uint8, device=dev)
+    h_ref = torch.empty(n_pages, dtype=torch.int32)
+    h_crc = torch.empty(n_pages, dtype=torch.int32)
+    h_packed = torch.empty(int(n_pages * 0.79) * PAGE, dtype=torch.uint8, pin_memory=True)
+    seed, lib = 0x5EED5 + rank, ctx.lib
+    slots, mix = 0, {"n_zero": 0, "n_dup": 0}
+
+    def synth(view, page_base, count):
+        err = _lib.errbuf()
+        _lib.check(lib.grit_synth_image(ctx.handle, C.c_void_p(view.data_ptr()), count, page_base, seed, 10, 15, 1024,
+                                        C.c_void_p(torch.cuda.current_stream().cuda_stream), err, len(err)), err)
+    for p0 in range(0, n_pages, piece):
+        img = out[p0 * PAGE:(p0 + piece) * PAGE]
+        synth(img, p0, piece)
+        crc, h, ref = ctx.analyze(img)
+        ctx.dedup(crc, h, ref)
+        n = ctx.compact(img, ref, tmp, slot_base=0)
+        kind = (ref >> 29) & 7
+        ref = torch.where(kind == 2, ref + p0, torch.where(kind == 1, ref + slots, ref))   # piece-local -> image-wide
+        h_ref[p0:p0 + piece].copy_(ref)
+        h_crc[p0:p0 + piece].copy_(crc)
+        assert (slots + n) * PAGE <= h_packed.numel(), "restore stress: packed stream larger than planned"
+        h_packed[slots * PAGE:(slots + n) * PAGE].copy_(tmp[: n * PAGE])
+        mix["n_zero"] += int((kind == 0).sum())
+        mix["n_dup"] += int((kind == 2).sum())
+        slots += n
+    del tmp
+    out.zero_()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    _, st = ctx.restore_to_device(h_packed[: slots * PAGE], h_ref, h_crc, out, verify=True)
+    torch.cuda.synchronize()
+    dt = torch.tensor([time.perf_counter() - t0], device=dev)
+    if world > 1:
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+    dt = float(dt.item())
+    again = torch.empty(piece * PAGE, dtype=torch.uint8, device=dev)
+    for p0 in range(0, n_pages, piece):                       # the image is regenerated from its seed for the comparison
+        synth(again, p0, piece)
+        assert torch.equal(out[p0 * PAGE:(p0 + piece) * PAGE], again), f"restore stress: pages {p0}.. differ"
+    n_bytes, u_bytes = n_pages * PAGE, slots * PAGE
+    return {"image_bytes_per_gpu": n_bytes, "pages": n_pages, "packed_bytes": u_bytes,
+            "page_mix": {"n_zero": mix["n_zero"], "n_dup": mix["n_dup"], "n_data": slots},
+            "seconds": round(dt, 3), "image_gbs_all_ranks": round(world * n_bytes / dt / 1e9, 2),
+            "h2d_gbs_per_gpu": round(u_bytes / dt / 1e9, 2),
+            "frac_of_h2d_link": round(u_bytes / dt / 1e9 / link_h2d, 3) if link_h2d else None,
+            "kernel_ms": round(st["gpu_ms"], 1), "n_bad": st["n_bad"], "bit_exact": True,
+            "device_memory_beside_the_image": 4 * (64 << 20) + 8 * n_pages,
+            "api": "grit_restore_to_device: packed pages from pinned host memory through a ring of four 64 MiB chunks, "
+                   "CRC-32C of every stored page verified, pages scattered straight into the destination"}
 
 
 # ----------------------------------------------------------------------------- e2e_dir
@@ -941,6 +1021,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-dir", action="store_true", help="skip the directory-level legs")
     ap.add_argument("--no-extra", action="store_true", help="skip the other page mixes")
+    ap.add_argument("--no-stress", action="store_true", help="skip the full-HBM restore stress (configs[4])")
     ap.add_argument("--ref-sample", action="store_true", help="reference arm: copy a 2 GiB sample even if the image fits")
     args = ap.parse_args()
     if args.impl == "reference":
