@@ -133,3 +133,38 @@ def test_product_never_imports_the_oracle():
             if f.endswith((".py", ".cu", ".cpp", ".h", ".cuh")):
                 text = open(os.path.join(d, f), errors="replace").read()
                 assert "oracle" not in text.lower(), f"{f} mentions the oracle"
+
+
+def test_agent_deps_and_gc_subcommands(tmp_path):
+    """grit-agent deps / gc (host work only): what a checkpoint needs, and which packed directories on a PV no kept
+    checkpoint needs any more.  Uses the golden packed directories: packed_child is an incremental pack on packed_base."""
+    import shutil
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "grit_b200", "csrc", "grit-agent")
+    pv = tmp_path / "pv" / "ns"
+    pv.mkdir(parents=True)
+    for n in ("packed_base", "packed_child"):
+        shutil.copytree(os.path.join(root, "tests", "golden", n), pv / n)
+    shutil.copytree(os.path.join(root, "tests", "golden", "packed_base"), pv / "orphan")
+    (pv / "not-a-checkpoint").mkdir()
+    (pv / "not-a-checkpoint" / "file").write_bytes(b"x")
+    r = subprocess.run([exe, "--action", "deps", "--src-dir", str(pv / "packed_child")], capture_output=True, text=True)
+    assert r.returncode == 0 and r.stdout.split() == [str(pv / "packed_base")], (r.stdout, r.stderr)
+    r = subprocess.run([exe, "--action", "gc", "--src-dir", str(tmp_path / "pv"), "--keep", str(pv / "packed_child"), "--dry-run"],
+                       capture_output=True, text=True)
+    assert r.returncode == 0 and f"would remove {pv / 'orphan'}" in r.stdout and "packed_base" not in r.stdout.split("gc:")[0]
+    assert (pv / "orphan").exists()
+    r = subprocess.run([exe, "--action", "gc", "--src-dir", str(tmp_path / "pv"), "--keep", str(pv / "packed_child")],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert not (pv / "orphan").exists() and (pv / "packed_base").exists() and (pv / "packed_child").exists()
+    assert (pv / "not-a-checkpoint" / "file").exists()                        # only packed directories are touched
+    # a kept checkpoint whose parent is gone cannot vouch for anything: nothing is deleted
+    shutil.rmtree(pv / "packed_base")
+    shutil.copytree(os.path.join(root, "tests", "golden", "packed_base"), pv / "other")
+    r = subprocess.run([exe, "--action", "gc", "--src-dir", str(tmp_path / "pv"), "--keep", str(pv / "packed_child")],
+                       capture_output=True, text=True)
+    assert r.returncode == 1 and (pv / "other").exists()
+    r = subprocess.run([exe, "--action", "gc", "--src-dir", str(tmp_path / "pv")], capture_output=True, text=True)
+    assert r.returncode == 1 and "--keep" in r.stderr

@@ -248,6 +248,18 @@ def test_cpp_grit_agent_binary(oracle, tmp_path):
     assert (host / "download-state").read_bytes() == b"Transfer Completed\n"
     os.remove(host / "download-state")
     assert tree_snapshot(str(host)) == tree_snapshot(str(src))
+    # the three actions the packed format adds: verify (GPU), and a statistics file for the Job to surface
+    sf = tmp_path / "stats.json"
+    r = subprocess.run([exe, "--action", "verify", "--src-dir", str(pv), "--stats-file", str(sf)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    import json
+    js = json.loads(sf.read_text())
+    assert js["action"] == "verify" and js["n_bad"] == 0 and js["n_pages"] > 2000 and js["bytes_logical"] > 0
+    with open(pv / "pages-000.bin", "r+b") as f:
+        f.seek(5 * PAGE + 1)
+        f.write(b"\x00\xFF\x00")
+    r = subprocess.run([exe, "--action", "verify", "--src-dir", str(pv)], capture_output=True, text=True)
+    assert r.returncode == 1 and "CRC" in r.stderr
     r = subprocess.run([exe, "--action", "migrate"], capture_output=True, text=True)
     assert r.returncode == 1 and "run grit-agent failed: unknown action migrate" in r.stderr      # app.go:40,68
 
