@@ -58,6 +58,14 @@ class Stats(C.Structure):
         return {n: getattr(self, n) for n, _ in self._fields_}
 
 
+class CriuStats(C.Structure):
+    _fields_ = [(n, C.c_uint64) for n in ("n_pagemaps", "entries_in", "entries_out", "pages_total", "pages_in_parent",
+                                          "bytes_written")]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
 # every symbol include/gritpack.h declares: name -> (restype, argtypes)
 _ERR = [C.c_char_p, C.c_size_t]
 _P, _U64, _U32, _I = C.c_void_p, C.c_uint64, C.c_uint32, C.c_int
@@ -97,6 +105,7 @@ SYMBOLS = {
     "grit_restore_dir": (_I, [C.c_char_p, C.c_char_p, C.POINTER(Opts), C.POINTER(Stats)] + _ERR),
     "grit_verify_dir": (_I, [C.c_char_p, C.POINTER(Opts), C.POINTER(Stats)] + _ERR),
     "grit_image_deps": (_I, [C.c_char_p, C.c_int, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t)] + _ERR),
+    "grit_criu_incremental": (_I, [C.c_char_p, C.c_char_p, C.c_char_p, C.POINTER(CriuStats)] + _ERR),
     "grit_write_sentinel": (_I, [C.c_char_p, C.c_char_p]),
 }
 

@@ -92,3 +92,14 @@ def VerifyData(packed_dir, **kw):
     o, st, err = _opts(**kw), Stats(), _lib.errbuf()
     _lib.check(lib.grit_verify_dir(os.fsencode(packed_dir), C.byref(o), C.byref(st), err, len(err)), err)
     return st.as_dict()
+
+
+def CriuIncremental(src_dir, packed_dir, out_dir):
+    """grit_criu_incremental: rewrites the pagemap-*.img / pages-*.img pairs of the CRIU image directory `src_dir`
+    (packed into `packed_dir` against a parent) as a native CRIU incremental image under `out_dir`: runs the GPU found
+    unchanged at the same virtual address in the parent become in_parent, only the other pages are kept."""
+    lib = _lib.load()
+    st, err = _lib.CriuStats(), _lib.errbuf()
+    _lib.check(lib.grit_criu_incremental(os.fsencode(src_dir), os.fsencode(packed_dir), os.fsencode(out_dir), C.byref(st),
+                                         err, len(err)), err)
+    return st.as_dict()

@@ -594,6 +594,9 @@ Opts read_opts(const grit_opts* o) {
   return r;
 }
 
+// criu-extents.txt: which stream pages belong to which CRIU pagemap entry (defined with the CRIU code at the end)
+int write_criu_extents(const std::string& src, const std::string& dst, const Manifest& m, std::string* msg);
+
 struct CtxGuard {
   grit_ctx* ctx = nullptr;
   void release() {
@@ -924,6 +927,7 @@ int grit_pack_dir(const char* src_dir, const char* dst_dir, const grit_opts* opt
   m.hashes_crc = grit_crc32c(0, hash.data(), m.n_pages * 8);
   if (int rc = write_file(dst + "/pagemap.bin", pagemap.data(), pagemap.size(), &msg)) return fail(err, errlen, rc, "%s", msg.c_str());
   if (int rc = write_file(dst + "/hashes.bin", hash.data(), m.n_pages * 8, &msg)) return fail(err, errlen, rc, "%s", msg.c_str());
+  if (int rc = write_criu_extents(src, dst, m, &msg)) return fail(err, errlen, rc, "%s", msg.c_str());
   // the manifest goes last, through a rename: its presence means the pack is complete
   const std::string enc = encode_manifest(m), tmp = dst + "/" + kManifest + ".tmp";
   if (int rc = write_file(tmp, enc.data(), enc.size(), &msg)) return fail(err, errlen, rc, "%s", msg.c_str());
@@ -1195,6 +1199,371 @@ int grit_image_deps(const char* dir, int recursive, char* out, size_t outlen, si
     w += d.size() + 1;
   }
   *w = 0;
+  return GRIT_OK;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------
+// CRIU-aware ingest.  The directory this library packs is a CRIU image directory
+// (pkg/gritagent/checkpoint/runtime.go:122-134 has CRIU write it); the reference treats it as opaque files.  CRIU
+// itself is not under /root/reference: the image format below is the one CRIU publishes (criu.org/Images, CRIU 3.x/4.x):
+//   pagemap-<id>.img   u32 0x54564319 (IMG_COMMON_MAGIC), u32 0x56084025 (PAGEMAP_MAGIC), then records
+//                      { u32 size; protobuf message of `size` bytes }: first a pagemap_head { uint32 pages_id = 1 },
+//                      then pagemap_entry { uint64 vaddr = 1; uint32 nr_pages = 2; bool in_parent = 3; uint32 flags = 4 }
+//                      with flags PE_PARENT 1, PE_LAZY 2, PE_PRESENT 4
+//   pages-<pages_id>.img   the raw 4 KiB pages of every entry that is present (not in_parent), in entry order
+// CRIU's own incremental dumps mark a run "in_parent" when the parent image holds the same virtual address range
+// unchanged; CRIU never fills that in here because the agent never names a parent
+// (cmd/containerd-shim-grit-v1/runc/container.go:107, process/init.go:192 plumb ParentPath, nothing sets it).
+// The page hashes computed on the GPU can: a page of pages-N.img whose packed reference is PARENT and whose parent
+// page is the page of the same virtual address in the parent's image is exactly a page CRIU would have left out.
+namespace {
+
+constexpr uint32_t kCriuCommonMagic = 0x54564319u, kCriuPagemapMagic = 0x56084025u;
+constexpr uint32_t kPeParent = 1, kPePresent = 4;
+const char* const kExtents = "criu-extents.txt";
+
+struct CriuEntry {
+  uint64_t vaddr = 0;
+  uint32_t nr_pages = 0, flags = 0;
+  bool in_parent = false;
+  bool has_flags = false;
+  bool present() const { return !(in_parent || (flags & kPeParent)); }
+};
+struct CriuPagemap {
+  uint32_t pages_id = 0;
+  std::vector<CriuEntry> entries;
+};
+
+bool get_varint(const unsigned char*& p, const unsigned char* end, uint64_t* v) {
+  *v = 0;
+  for (int shift = 0; p < end && shift < 64; shift += 7) {
+    const unsigned char b = *p++;
+    *v |= (uint64_t)(b & 0x7F) << shift;
+    if (!(b & 0x80)) return true;
+  }
+  return false;
+}
+void put_varint(std::string* b, uint64_t v) {
+  while (v >= 0x80) {
+    b->push_back((char)(v | 0x80));
+    v >>= 7;
+  }
+  b->push_back((char)v);
+}
+// one protobuf message: varint fields into f[1..4], everything else skipped
+bool parse_fields(const unsigned char* p, const unsigned char* end, uint64_t (&f)[5], bool (&have)[5]) {
+  while (p < end) {
+    uint64_t key, v;
+    if (!get_varint(p, end, &key)) return false;
+    const uint32_t field = (uint32_t)(key >> 3), wt = (uint32_t)(key & 7);
+    if (wt == 0) {
+      if (!get_varint(p, end, &v)) return false;
+      if (field >= 1 && field <= 4) f[field] = v, have[field] = true;
+    } else if (wt == 2) {
+      if (!get_varint(p, end, &v) || v > (uint64_t)(end - p)) return false;
+      p += v;
+    } else if (wt == 1 || wt == 5) {
+      const size_t n = wt == 1 ? 8 : 4;
+      if ((size_t)(end - p) < n) return false;
+      p += n;
+    } else {
+      return false;
+    }
+  }
+  return true;
+}
+
+// false: not a pagemap image (the file is then just opaque bytes to the packer)
+bool parse_criu_pagemap(const std::string& bytes, CriuPagemap* out) {
+  if (bytes.size() < 8) return false;
+  uint32_t m[2];
+  memcpy(m, bytes.data(), 8);
+  if (m[0] != kCriuCommonMagic || m[1] != kCriuPagemapMagic) return false;
+  const unsigned char* p = reinterpret_cast<const unsigned char*>(bytes.data()) + 8;
+  const unsigned char* end = p + bytes.size() - 8;
+  bool head = true;
+  while (p < end) {
+    if (end - p < 4) return false;
+    uint32_t size;
+    memcpy(&size, p, 4);
+    p += 4;
+    if (size > (uint64_t)(end - p)) return false;
+    uint64_t f[5] = {};
+    bool have[5] = {};
+    if (!parse_fields(p, p + size, f, have)) return false;
+    p += size;
+    if (head) {
+      if (!have[1]) return false;
+      out->pages_id = (uint32_t)f[1];
+      head = false;
+      continue;
+    }
+    if (!have[1] || !have[2]) return false;
+    CriuEntry e;
+    e.vaddr = f[1];
+    e.nr_pages = (uint32_t)f[2];
+    e.in_parent = have[3] && f[3];
+    e.has_flags = have[4];
+    e.flags = (uint32_t)f[4];
+    out->entries.push_back(e);
+  }
+  return !head;
+}
+
+std::string encode_criu_pagemap(const CriuPagemap& pm) {
+  std::string b;
+  put(&b, kCriuCommonMagic);
+  put(&b, kCriuPagemapMagic);
+  auto record = [&](const std::string& msg) {
+    put<uint32_t>(&b, (uint32_t)msg.size());
+    b += msg;
+  };
+  std::string m;
+  m.push_back(0x08);
+  put_varint(&m, pm.pages_id);
+  record(m);
+  for (const auto& e : pm.entries) {
+    m.clear();
+    m.push_back(0x08);
+    put_varint(&m, e.vaddr);
+    m.push_back(0x10);
+    put_varint(&m, e.nr_pages);
+    if (e.in_parent) {
+      m.push_back(0x18);
+      put_varint(&m, 1);
+    }
+    if (e.has_flags || e.in_parent) {
+      m.push_back(0x20);
+      put_varint(&m, e.flags);
+    }
+    record(m);
+  }
+  return b;
+}
+
+}  // namespace
+
+namespace {
+
+struct ExtentFile {
+  std::string pagemap_path, pages_path;  // relative to the tree root
+  uint64_t first_page = 0;               // stream page of the pages file's first page
+  CriuPagemap pm;
+};
+
+std::string dir_of(const std::string& rel) {
+  const size_t s = rel.find_last_of('/');
+  return s == std::string::npos ? std::string() : rel.substr(0, s + 1);
+}
+
+// Which stream pages belong to which pagemap entry: every pagemap-*.img of the tree that parses, with the pages file
+// its head names.  Written beside the packed image by grit_pack_dir; an image without CRIU page maps gets none.
+int collect_extents(const std::string& src, const Manifest& m, std::vector<ExtentFile>* out) {
+  for (const auto& e : m.entries) {
+    if (e.type != 1) continue;
+    const size_t slash = e.path.find_last_of('/');
+    const std::string name = slash == std::string::npos ? e.path : e.path.substr(slash + 1);
+    if (name.compare(0, 8, "pagemap-") != 0 || name.size() < 5 || name.compare(name.size() - 4, 4, ".img") != 0) continue;
+    if (e.size > (64u << 20)) continue;
+    std::string bytes, msg;
+    if (read_file(src + "/" + e.path, &bytes, &msg)) continue;
+    ExtentFile x;
+    if (!parse_criu_pagemap(bytes, &x.pm)) continue;
+    x.pagemap_path = e.path;
+    x.pages_path = dir_of(e.path) + "pages-" + std::to_string(x.pm.pages_id) + ".img";
+    uint64_t present = 0;
+    for (const auto& pe : x.pm.entries)
+      if (pe.present()) present += pe.nr_pages;
+    bool found = false;
+    for (const auto& f : m.entries)
+      if (f.type == 1 && f.path == x.pages_path) {
+        found = f.size == present * kPage;  // the page map and its pages file must agree
+        x.first_page = f.first_page;
+      }
+    if (found) out->push_back(std::move(x));
+  }
+  return GRIT_OK;
+}
+
+std::string encode_extents(const std::vector<ExtentFile>& xs) {
+  std::string b = "gritpack-criu-extents 1\n";
+  char line[256];
+  for (const auto& x : xs) {
+    // paths go last on their own lines: they may hold spaces
+    snprintf(line, sizeof line, "pagemap %u %llu %zu\n", x.pm.pages_id, (unsigned long long)x.first_page, x.pm.entries.size());
+    b += line;
+    b += x.pagemap_path + "\n" + x.pages_path + "\n";
+    for (const auto& e : x.pm.entries) {
+      snprintf(line, sizeof line, "e %llx %u %u %d %d\n", (unsigned long long)e.vaddr, e.nr_pages, e.flags, e.in_parent ? 1 : 0,
+               e.has_flags ? 1 : 0);
+      b += line;
+    }
+  }
+  return b;
+}
+
+int load_extents(const std::string& packed_dir, std::vector<ExtentFile>* out, std::string* msg) {
+  std::string b;
+  if (int rc = read_file(packed_dir + "/" + kExtents, &b, msg)) return rc;
+  size_t pos = 0;
+  auto next_line = [&](std::string* l) {
+    if (pos >= b.size()) return false;
+    const size_t e = b.find('\n', pos);
+    *l = b.substr(pos, (e == std::string::npos ? b.size() : e) - pos);
+    pos = e == std::string::npos ? b.size() : e + 1;
+    return true;
+  };
+  std::string l;
+  if (!next_line(&l) || l != "gritpack-criu-extents 1") return *msg = packed_dir + "/" + kExtents + ": unknown format", GRIT_EFORMAT;
+  while (next_line(&l)) {
+    ExtentFile x;
+    unsigned long long first = 0;
+    size_t n = 0;
+    if (sscanf(l.c_str(), "pagemap %u %llu %zu", &x.pm.pages_id, &first, &n) != 3 || !next_line(&x.pagemap_path) ||
+        !next_line(&x.pages_path))
+      return *msg = packed_dir + "/" + kExtents + ": damaged", GRIT_EFORMAT;
+    x.first_page = first;
+    for (size_t i = 0; i < n; i++) {
+      CriuEntry e;
+      unsigned long long va = 0;
+      int inp = 0, hf = 0;
+      if (!next_line(&l) || sscanf(l.c_str(), "e %llx %u %u %d %d", &va, &e.nr_pages, &e.flags, &inp, &hf) != 5)
+        return *msg = packed_dir + "/" + kExtents + ": damaged", GRIT_EFORMAT;
+      e.vaddr = va;
+      e.in_parent = inp != 0;
+      e.has_flags = hf != 0;
+      x.pm.entries.push_back(e);
+    }
+    out->push_back(std::move(x));
+  }
+  return GRIT_OK;
+}
+
+int write_criu_extents(const std::string& src, const std::string& dst, const Manifest& m, std::string* msg) {
+  std::vector<ExtentFile> xs;
+  collect_extents(src, m, &xs);
+  const std::string path = dst + "/" + kExtents;
+  if (xs.empty()) {
+    unlink(path.c_str());  // a re-run over an older pack of another tree
+    return GRIT_OK;
+  }
+  const std::string enc = encode_extents(xs);
+  return write_file(path, enc.data(), enc.size(), msg);
+}
+
+}  // namespace
+
+extern "C" {
+
+int grit_criu_incremental(const char* src_dir, const char* packed_dir, const char* out_dir, grit_criu_stats* stats,
+                          char* err, size_t errlen) {
+  if (!src_dir || !packed_dir || !out_dir) return fail(err, errlen, GRIT_EINVAL, "null directory");
+  const std::string src = src_dir, packed = packed_dir, out = out_dir;
+  std::string msg;
+  grit_criu_stats st{};
+  Manifest m;
+  if (!has_manifest(packed)) return fail(err, errlen, GRIT_EFORMAT, "%s holds no %s", packed_dir, kManifest);
+  if (int rc = load_manifest(packed, &m, &msg)) return fail(err, errlen, rc, "%s", msg.c_str());
+  if (m.parent.empty()) return fail(err, errlen, GRIT_EINVAL, "%s was packed without a parent: nothing can be left to one", packed_dir);
+  std::vector<uint32_t> ref, crc;
+  if (int rc = load_pagemap(packed, m, &ref, &crc, &msg)) return fail(err, errlen, rc, "%s", msg.c_str());
+  std::vector<ExtentFile> mine, theirs;
+  if (int rc = load_extents(packed, &mine, &msg)) return fail(err, errlen, rc, "%s", msg.c_str());
+  if (int rc = load_extents(resolve_parent(packed, m.parent), &theirs, &msg)) return fail(err, errlen, rc, "parent: %s", msg.c_str());
+
+  for (const auto& x : mine) {
+    // the parent's pages of the same page map, by virtual address: (vaddr, pages, first stream page), sorted
+    struct Run {
+      uint64_t vaddr, nr, first;
+    };
+    std::vector<Run> runs;
+    for (const auto& y : theirs)
+      if (y.pagemap_path == x.pagemap_path) {
+        uint64_t fp = y.first_page;
+        for (const auto& e : y.pm.entries)
+          if (e.present()) {
+            runs.push_back({e.vaddr, e.nr_pages, fp});
+            fp += e.nr_pages;
+          }
+      }
+    std::sort(runs.begin(), runs.end(), [](const Run& a, const Run& b) { return a.vaddr < b.vaddr; });
+    auto parent_page_at = [&](uint64_t vaddr, uint64_t* page) {
+      auto it = std::upper_bound(runs.begin(), runs.end(), vaddr, [](uint64_t v, const Run& r) { return v < r.vaddr; });
+      if (it == runs.begin()) return false;
+      --it;
+      if (vaddr >= it->vaddr + it->nr * kPage) return false;
+      *page = it->first + (vaddr - it->vaddr) / kPage;
+      return true;
+    };
+    CriuPagemap outpm;
+    outpm.pages_id = x.pm.pages_id;
+    std::vector<uint64_t> keep;  // pages of the source pages file that stay, in order
+    uint64_t file_page = 0;
+    for (const auto& e : x.pm.entries) {
+      st.entries_in++;
+      if (!e.present()) {  // CRIU's own in_parent run: passed through
+        outpm.entries.push_back(e);
+        continue;
+      }
+      uint32_t i = 0;
+      while (i < e.nr_pages) {
+        auto in_parent = [&](uint32_t k) {
+          const uint64_t p = x.first_page + file_page + k;
+          uint64_t q;
+          return p < m.n_pages && GRIT_REF_KIND(ref[p]) == GRIT_KIND_PARENT && parent_page_at(e.vaddr + (uint64_t)k * kPage, &q) &&
+                 q == GRIT_REF_VALUE(ref[p]);
+        };
+        const bool par = in_parent(i);
+        uint32_t j = i + 1;
+        while (j < e.nr_pages && in_parent(j) == par) j++;
+        CriuEntry o = e;
+        o.vaddr = e.vaddr + (uint64_t)i * kPage;
+        o.nr_pages = j - i;
+        if (par) {
+          o.in_parent = true;
+          o.has_flags = true;
+          o.flags = (e.flags & ~kPePresent) | kPeParent;
+          st.pages_in_parent += j - i;
+        } else {
+          for (uint32_t k = i; k < j; k++) keep.push_back(file_page + k);
+        }
+        outpm.entries.push_back(o);
+        i = j;
+      }
+      file_page += e.nr_pages;
+      st.pages_total += e.nr_pages;
+    }
+    st.entries_out += outpm.entries.size();
+    st.n_pagemaps++;
+    // the rewritten pair
+    const std::string pm_path = out + "/" + x.pagemap_path, pg_path = out + "/" + x.pages_path;
+    if (mkdir_all(out + "/" + dir_of(x.pagemap_path)) != 0) return fail(err, errlen, GRIT_EIO, "%s", errno_msg("mkdir", out).c_str());
+    const std::string enc = encode_criu_pagemap(outpm);
+    if (int rc = write_file(pm_path, enc.data(), enc.size(), &msg)) return fail(err, errlen, rc, "%s", msg.c_str());
+    const int in = open((src + "/" + x.pages_path).c_str(), O_RDONLY | O_CLOEXEC);
+    const int of = open(pg_path.c_str(), O_WRONLY | O_CREAT | O_TRUNC | O_CLOEXEC, 0600);
+    if (in < 0 || of < 0) {
+      if (in >= 0) close(in);
+      if (of >= 0) close(of);
+      return fail(err, errlen, GRIT_EIO, "%s", errno_msg("open", in < 0 ? src + "/" + x.pages_path : pg_path).c_str());
+    }
+    std::vector<char> buf(256 * kPage);
+    bool bad = false;
+    for (size_t a = 0; a < keep.size() && !bad;) {  // runs of consecutive pages move together
+      size_t b = a + 1;
+      while (b < keep.size() && keep[b] == keep[b - 1] + 1 && b - a < 256) b++;
+      const size_t n = (b - a) * kPage;
+      bad = pread(in, buf.data(), n, (off_t)(keep[a] * kPage)) != (ssize_t)n || write(of, buf.data(), n) != (ssize_t)n;
+      a = b;
+    }
+    close(in);
+    bad = (close(of) != 0) || bad;
+    if (bad) return fail(err, errlen, GRIT_EIO, "%s", errno_msg("copy", pg_path).c_str());
+    st.bytes_written += keep.size() * kPage + enc.size();
+  }
+  if (stats) *stats = st;
   return GRIT_OK;
 }
 

@@ -380,6 +380,34 @@ int grit_verify_dir(const char *src_dir, const grit_opts *opts,
 int grit_image_deps(const char *dir, int recursive, char *out, size_t outlen,
                     size_t *needed, char *err, size_t errlen);
 
+/* ---- CRIU-aware ingest ---------------------------------------
+ * The tree the agent uploads is a CRIU image directory written at
+ * pkg/gritagent/checkpoint/runtime.go:122-134; the reference copies it as
+ * opaque files.  grit_pack_dir parses every pagemap-<id>.img it finds (CRIU's
+ * published image format; CRIU is not part of the reference tree) and records
+ * beside the packed image, in criu-extents.txt, which pages of the page stream
+ * belong to which virtual-address run of which pages-<id>.img.
+ *
+ * grit_criu_incremental turns an incremental pack into what CRIU itself calls
+ * an incremental image: for every page map of the tree src_dir (which was
+ * packed into packed_dir with a parent) it writes, under out_dir at the same
+ * relative paths, a pagemap-<id>.img whose runs are marked in_parent wherever
+ * the GPU found the page unchanged at the SAME virtual address in the parent
+ * (packed reference PARENT to exactly that page), and a pages-<id>.img holding
+ * only the remaining pages.  Together with a `parent` link to the previous
+ * image directory that is a native CRIU parent chain -- the link the shim
+ * plumbs but nobody sets (cmd/containerd-shim-grit-v1/runc/container.go:107,
+ * process/init.go:192).  Host work only; the GPU's part is the page map
+ * packed_dir already holds.  The other files of the image are not rewritten. */
+typedef struct grit_criu_stats {
+  uint64_t n_pagemaps, entries_in, entries_out;
+  uint64_t pages_total, pages_in_parent; /* pages of present runs; those left to the parent */
+  uint64_t bytes_written;
+} grit_criu_stats;
+int grit_criu_incremental(const char *src_dir, const char *packed_dir,
+                          const char *out_dir, grit_criu_stats *stats,
+                          char *err, size_t errlen);
+
 /* CreateSentinelFile (copy.go:92-102): dir/name holding "Transfer Completed\n". */
 int grit_write_sentinel(const char *dir, const char *name);
 
