@@ -1457,6 +1457,22 @@ int write_criu_extents(const std::string& src, const std::string& dst, const Man
 
 extern "C" {
 
+int grit_criu_pagemap_info(const char* path, uint32_t* pages_id, uint64_t* n_entries, uint64_t* pages_present,
+                           uint64_t* pages_in_parent, char* err, size_t errlen) {
+  if (!path) return fail(err, errlen, GRIT_EINVAL, "null path");
+  std::string bytes, msg;
+  if (int rc = read_file(path, &bytes, &msg)) return fail(err, errlen, rc, "%s", msg.c_str());
+  CriuPagemap pm;
+  if (!parse_criu_pagemap(bytes, &pm)) return fail(err, errlen, GRIT_EFORMAT, "%s: not a CRIU pagemap image", path);
+  uint64_t present = 0, inpar = 0;
+  for (const auto& e : pm.entries) (e.present() ? present : inpar) += e.nr_pages;
+  if (pages_id) *pages_id = pm.pages_id;
+  if (n_entries) *n_entries = pm.entries.size();
+  if (pages_present) *pages_present = present;
+  if (pages_in_parent) *pages_in_parent = inpar;
+  return GRIT_OK;
+}
+
 int grit_criu_incremental(const char* src_dir, const char* packed_dir, const char* out_dir, grit_criu_stats* stats,
                           char* err, size_t errlen) {
   if (!src_dir || !packed_dir || !out_dir) return fail(err, errlen, GRIT_EINVAL, "null directory");
@@ -1471,7 +1487,16 @@ int grit_criu_incremental(const char* src_dir, const char* packed_dir, const cha
   if (int rc = load_pagemap(packed, m, &ref, &crc, &msg)) return fail(err, errlen, rc, "%s", msg.c_str());
   std::vector<ExtentFile> mine, theirs;
   if (int rc = load_extents(packed, &mine, &msg)) return fail(err, errlen, rc, "%s", msg.c_str());
-  if (int rc = load_extents(resolve_parent(packed, m.parent), &theirs, &msg)) return fail(err, errlen, rc, "parent: %s", msg.c_str());
+  const std::string parent_dir = resolve_parent(packed, m.parent);
+  if (int rc = load_extents(parent_dir, &theirs, &msg)) return fail(err, errlen, rc, "parent: %s", msg.c_str());
+  // A PARENT reference names the lowest parent page with that content; the page at the same address may be a later
+  // copy of it.  Equal (hash64, CRC-32C) in the parent's own tables is what "the same page" means here.
+  Manifest pm;
+  std::vector<uint32_t> p_ref, p_crc;
+  std::vector<uint64_t> p_hash;
+  if (int rc = load_manifest(parent_dir, &pm, &msg)) return fail(err, errlen, rc, "parent: %s", msg.c_str());
+  if (int rc = load_pagemap(parent_dir, pm, &p_ref, &p_crc, &msg)) return fail(err, errlen, rc, "parent: %s", msg.c_str());
+  if (int rc = load_hashes(parent_dir, pm, &p_hash, &msg)) return fail(err, errlen, rc, "parent: %s", msg.c_str());
 
   for (const auto& x : mine) {
     // the parent's pages of the same page map, by virtual address: (vaddr, pages, first stream page), sorted
@@ -1512,8 +1537,10 @@ int grit_criu_incremental(const char* src_dir, const char* packed_dir, const cha
         auto in_parent = [&](uint32_t k) {
           const uint64_t p = x.first_page + file_page + k;
           uint64_t q;
-          return p < m.n_pages && GRIT_REF_KIND(ref[p]) == GRIT_KIND_PARENT && parent_page_at(e.vaddr + (uint64_t)k * kPage, &q) &&
-                 q == GRIT_REF_VALUE(ref[p]);
+          if (p >= m.n_pages || GRIT_REF_KIND(ref[p]) != GRIT_KIND_PARENT || !parent_page_at(e.vaddr + (uint64_t)k * kPage, &q))
+            return false;
+          const uint64_t owner = GRIT_REF_VALUE(ref[p]);
+          return q < pm.n_pages && owner < pm.n_pages && p_hash[q] == p_hash[owner] && p_crc[q] == p_crc[owner];
         };
         const bool par = in_parent(i);
         uint32_t j = i + 1;

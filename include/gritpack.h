@@ -404,6 +404,12 @@ typedef struct grit_criu_stats {
   uint64_t pages_total, pages_in_parent; /* pages of present runs; those left to the parent */
   uint64_t bytes_written;
 } grit_criu_stats;
+/* What a pagemap-<id>.img says: the pages file it belongs to, its runs, how
+ * many pages are present in that file and how many are left to a parent.
+ * GRIT_EFORMAT when the file is not a CRIU page map.  Host work only. */
+int grit_criu_pagemap_info(const char *path, uint32_t *pages_id,
+                           uint64_t *n_entries, uint64_t *pages_present,
+                           uint64_t *pages_in_parent, char *err, size_t errlen);
 int grit_criu_incremental(const char *src_dir, const char *packed_dir,
                           const char *out_dir, grit_criu_stats *stats,
                           char *err, size_t errlen);
