@@ -105,6 +105,12 @@ SYMBOLS = {
     "grit_restore_dir": (_I, [C.c_char_p, C.c_char_p, C.POINTER(Opts), C.POINTER(Stats)] + _ERR),
     "grit_verify_dir": (_I, [C.c_char_p, C.POINTER(Opts), C.POINTER(Stats)] + _ERR),
     "grit_image_deps": (_I, [C.c_char_p, C.c_int, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t)] + _ERR),
+    "grit_image_open": (_I, [C.c_char_p, C.POINTER(Opts), C.POINTER(_P)] + _ERR),
+    "grit_image_close": (None, [_P]),
+    "grit_image_stat": (_I, [_P, C.c_char_p, C.POINTER(_U64), C.POINTER(_U32), C.POINTER(_U64)] + _ERR),
+    "grit_image_read": (C.c_int64, [_P, C.c_char_p, _U64, _U64, _P] + _ERR),
+    "grit_image_read_pages": (_I, [_P, _U64, _U64, _P, _I] + _ERR),
+    "grit_image_resident_slots": (_U64, [_P]),
     "grit_criu_pagemap_info": (_I, [C.c_char_p, C.POINTER(_U32), C.POINTER(_U64), C.POINTER(_U64), C.POINTER(_U64)] + _ERR),
     "grit_criu_incremental": (_I, [C.c_char_p, C.c_char_p, C.c_char_p, C.POINTER(CriuStats)] + _ERR),
     "grit_write_sentinel": (_I, [C.c_char_p, C.c_char_p]),

@@ -103,3 +103,51 @@ def CriuIncremental(src_dir, packed_dir, out_dir):
     _lib.check(lib.grit_criu_incremental(os.fsencode(src_dir), os.fsencode(packed_dir), os.fsencode(out_dir), C.byref(st),
                                          err, len(err)), err)
     return st.as_dict()
+
+
+class PackedImage:
+    """grit_image: a packed checkpoint kept open and served on demand (what a lazy-pages server or a FUSE view of
+    the checkpoint would sit on).  read() is pread on a file of the tree; read_pages() fills a CUDA tensor."""
+
+    def __init__(self, packed_dir, **kw):
+        self.lib = _lib.load()
+        o, h, err = _opts(**kw), C.c_void_p(), _lib.errbuf()
+        _lib.check(self.lib.grit_image_open(os.fsencode(packed_dir), C.byref(o), C.byref(h), err, len(err)), err)
+        self.handle = h
+
+    def close(self):
+        if getattr(self, "handle", None):
+            self.lib.grit_image_close(self.handle)
+            self.handle = None
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def stat(self, relpath):
+        size, mode, first, err = C.c_uint64(), C.c_uint32(), C.c_uint64(), _lib.errbuf()
+        _lib.check(self.lib.grit_image_stat(self.handle, os.fsencode(relpath), C.byref(size), C.byref(mode), C.byref(first),
+                                            err, len(err)), err)
+        return dict(size=size.value, mode=mode.value, first_page=first.value)
+
+    def read(self, relpath, offset, length):
+        buf, err = C.create_string_buffer(max(length, 1)), _lib.errbuf()
+        n = self.lib.grit_image_read(self.handle, os.fsencode(relpath), offset, length, buf, err, len(err))
+        if n < 0:
+            _lib.check(int(n), err)
+        return buf.raw[:n]
+
+    def read_pages(self, page0, n_pages, out):
+        """out: a CUDA uint8 tensor on the image's device, or a CPU uint8 tensor."""
+        err = _lib.errbuf()
+        _lib.check(self.lib.grit_image_read_pages(self.handle, page0, n_pages, C.c_void_p(out.data_ptr()),
+                                                  1 if out.is_cuda else 0, err, len(err)), err)
+        return out
+
+    @property
+    def resident_slots(self):
+        return int(self.lib.grit_image_resident_slots(self.handle))

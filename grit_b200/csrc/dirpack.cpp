@@ -30,6 +30,7 @@
 #include <cstring>
 #include <deque>
 #include <functional>
+#include <memory>
 #include <mutex>
 #include <string>
 #include <thread>
@@ -1592,6 +1593,250 @@ int grit_criu_incremental(const char* src_dir, const char* packed_dir, const cha
   }
   if (stats) *stats = st;
   return GRIT_OK;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------
+// Serving a packed checkpoint page by page.  The reference's restore lands the whole tree on local
+// disk before the runtime may start (restore.go:16-20; containerd waits for the sentinel,
+// contrib/containerd/grit-interceptor.diff:146-165), then CRIU reads it all again
+// (cmd/containerd-shim-grit-v1/process/init_state.go:163).  A grit_image keeps the packed checkpoint open instead: the
+// stored pages stream into HBM in the background, and any page range, or any byte range of any file of the tree,
+// can be asked for as soon as the slots it needs have arrived -- restored and CRC-checked on the GPU, delivered to
+// host memory (a lazy-pages server answering CRIU's page faults, a FUSE view of the tree) or left in device memory
+// (device state that never needs to touch the host again).
+struct grit_image {
+  CtxGuard cg;
+  std::string dir;
+  Manifest m;
+  std::vector<uint32_t> ref, crc;
+  ImageCache cache;  // parent / lower-rank images this one refers to, restored on the device
+  PeerImages imgs{};
+  PageStore store;
+  void* d_packed = nullptr;
+  uint32_t *d_ref = nullptr, *d_crc = nullptr;
+  void* d_out = nullptr;    // one chunk of restored pages
+  void* h_stage = nullptr;  // pinned, one chunk
+  uint64_t chunk_pages = 0;
+  int verify = 1;
+  // background upload of the stored pages, in slot order
+  std::thread uploader;
+  std::mutex mu;
+  std::condition_variable cv;
+  uint64_t slots_resident = 0;
+  int upload_rc = 0;
+  bool stop = false;
+  std::mutex read_mu;  // one read at a time
+  uint64_t reads = 0, pages_served = 0;
+  ~grit_image() {
+    {
+      std::lock_guard<std::mutex> l(mu);
+      stop = true;
+    }
+    cv.notify_all();
+    if (uploader.joinable()) uploader.join();
+    if (cg.ctx) {
+      cudaSetDevice(cg.ctx->device);
+      cudaDeviceSynchronize();
+    }
+    cudaFree(d_packed);
+    cudaFree(d_ref);
+    cudaFree(d_crc);
+    cudaFree(d_out);
+    cudaFreeHost(h_stage);
+    cache.release();
+  }
+};
+
+extern "C" {
+
+int grit_image_open(const char* packed_dir, const grit_opts* opts, grit_image** out, char* err, size_t errlen) {
+  if (!packed_dir || !out) return fail(err, errlen, GRIT_EINVAL, "null argument");
+  *out = nullptr;
+  const Opts o = read_opts(opts);
+  std::string msg;
+  if (!has_manifest(packed_dir)) return fail(err, errlen, GRIT_EFORMAT, "%s holds no %s", packed_dir, kManifest);
+  std::unique_ptr<grit_image> im(new (std::nothrow) grit_image());
+  if (!im) return fail(err, errlen, GRIT_ENOMEM, "out of host memory");
+  im->dir = packed_dir;
+  im->verify = o.verify ? 1 : 0;
+  if (int rc = load_manifest(im->dir, &im->m, &msg)) return fail(err, errlen, rc, "%s", msg.c_str());
+  if (int rc = load_pagemap(im->dir, im->m, &im->ref, &im->crc, &msg)) return fail(err, errlen, rc, "%s", msg.c_str());
+  if (int rc = grit_ctx_create(o.device, &im->cg.ctx, err, errlen)) return rc;
+  grit_ctx* ctx = im->cg.ctx;
+  const Manifest& m = im->m;
+  const ImageCache::Img* parent = nullptr;
+  grit_stats st{};
+  if (int rc = load_dependencies(ctx, im->dir, m, im->ref, im->verify, &im->cache, 0, &st, &parent, &im->imgs, &msg))
+    return fail(err, errlen, rc, "%s", msg.c_str());
+  im->imgs.parent = parent ? static_cast<const unsigned char*>(parent->d) : nullptr;
+  im->imgs.parent_pages = parent ? parent->pages : 0;
+  im->store.dir = im->dir;
+  im->store.k = m.n_shards;
+  im->store.stripe = m.stripe_slots;
+  if (int rc = im->store.open_all(false, &msg)) return fail(err, errlen, rc, "%s", msg.c_str());
+  if (int rc = im->store.check_sizes(m.n_slots, &msg)) return fail(err, errlen, rc, "%s", msg.c_str());
+  im->chunk_pages = (16ull << 20) / kPage;
+  GRIT_CUDA(cudaMalloc(&im->d_packed, std::max<uint64_t>(m.n_slots, 1) * kPage));
+  GRIT_CUDA(cudaMalloc(&im->d_ref, std::max<uint64_t>(m.n_pages, 1) * 4));
+  GRIT_CUDA(cudaMalloc(&im->d_crc, std::max<uint64_t>(m.n_pages, 1) * 4));
+  GRIT_CUDA(cudaMalloc(&im->d_out, im->chunk_pages * kPage));
+  GRIT_CUDA(cudaMallocHost(&im->h_stage, im->chunk_pages * kPage));
+  GRIT_CUDA(cudaMemcpy(im->d_ref, im->ref.data(), m.n_pages * 4, cudaMemcpyHostToDevice));
+  GRIT_CUDA(cudaMemcpy(im->d_crc, im->crc.data(), m.n_pages * 4, cudaMemcpyHostToDevice));
+  grit_image* g = im.get();
+  const unsigned io_threads = o.io_threads;
+  g->uploader = std::thread([g, io_threads] {
+    cudaSetDevice(g->cg.ctx->device);
+    const uint64_t step = (8ull << 20) / kPage, n_slots = g->m.n_slots;
+    void* h[2] = {nullptr, nullptr};
+    cudaEvent_t ev[2] = {nullptr, nullptr};
+    int rc = 0;
+    for (int b = 0; b < 2 && !rc; b++)
+      if (cudaMallocHost(&h[b], step * kPage) != cudaSuccess || cudaEventCreateWithFlags(&ev[b], cudaEventDisableTiming) != cudaSuccess)
+        rc = GRIT_ECUDA;
+    IoPool pool(io_threads);
+    uint64_t enq[2] = {0, 0};  // slots covered once buffer b's copy has landed
+    const uint64_t n_chunks = (n_slots + step - 1) / step;
+    for (uint64_t k = 0; k < n_chunks && !rc; k++) {
+      const int b = (int)(k & 1);
+      if (k >= 2) {  // buffer b's previous copy must have landed before it is refilled: that also moves the watermark
+        if (cudaEventSynchronize(ev[b]) != cudaSuccess) rc = GRIT_ECUDA;
+        std::lock_guard<std::mutex> l(g->mu);
+        g->slots_resident = std::max(g->slots_resident, enq[b]);
+        g->cv.notify_all();
+      }
+      {
+        std::lock_guard<std::mutex> l(g->mu);
+        if (g->stop) break;
+      }
+      const uint64_t s0 = k * step, n = std::min(step, n_slots - s0);
+      if (!rc && g->store.io(s0, n, static_cast<char*>(h[b]), &pool, false)) rc = GRIT_EIO;
+      if (!rc && cudaMemcpyAsync(static_cast<char*>(g->d_packed) + s0 * kPage, h[b], n * kPage, cudaMemcpyHostToDevice,
+                                 g->cg.ctx->h2d) != cudaSuccess)
+        rc = GRIT_ECUDA;
+      if (!rc && cudaEventRecord(ev[b], g->cg.ctx->h2d) != cudaSuccess) rc = GRIT_ECUDA;
+      enq[b] = s0 + n;
+    }
+    cudaStreamSynchronize(g->cg.ctx->h2d);
+    for (int b = 0; b < 2; b++) {
+      if (h[b]) cudaFreeHost(h[b]);
+      if (ev[b]) cudaEventDestroy(ev[b]);
+    }
+    std::lock_guard<std::mutex> l(g->mu);
+    if (rc) g->upload_rc = rc;
+    else if (!g->stop) g->slots_resident = n_slots;
+    g->cv.notify_all();
+  });
+  *out = im.release();
+  return GRIT_OK;
+}
+
+void grit_image_close(grit_image* im) { delete im; }
+
+}  // extern "C"
+
+namespace {
+
+// pages [p0, p1) of the image -> dst (host memory, or device memory of the image's GPU)
+int image_read_pages(grit_image* im, uint64_t p0, uint64_t p1, char* dst, bool dst_on_device, uint64_t skip_first,
+                     uint64_t len_bytes, char* err, size_t errlen) {
+  // skip_first / len_bytes: the byte window of the page run that the caller wants (file reads are not page aligned)
+  grit_ctx* ctx = im->cg.ctx;
+  const Manifest& m = im->m;
+  GRIT_CUDA(cudaSetDevice(ctx->device));
+  std::lock_guard<std::mutex> g(im->read_mu);
+  uint64_t done_bytes = 0;
+  for (uint64_t a = p0; a < p1; a += im->chunk_pages) {
+    const uint64_t b = std::min(p1, a + im->chunk_pages);
+    uint64_t need = 0;  // slots [0, need) must be on the device
+    for (uint64_t p = a; p < b; p++) {
+      uint32_t x = im->ref[p];
+      if (GRIT_REF_KIND(x) == GRIT_KIND_DUP && GRIT_REF_VALUE(x) < m.n_pages) x = im->ref[GRIT_REF_VALUE(x)];
+      if (GRIT_REF_KIND(x) == GRIT_KIND_DATA) need = std::max<uint64_t>(need, (uint64_t)GRIT_REF_VALUE(x) + 1);
+    }
+    need = std::min(need, m.n_slots);
+    {
+      std::unique_lock<std::mutex> l(im->mu);
+      im->cv.wait(l, [&] { return im->upload_rc || im->slots_resident >= need; });
+      if (im->upload_rc) return fail(err, errlen, im->upload_rc, "%s: reading the stored pages failed", im->dir.c_str());
+    }
+    std::lock_guard<std::mutex> cl(ctx->mu);
+    cudaStream_t s = ctx->stream;
+    if (int rc = reset_counters(ctx, s, err, errlen)) return rc;
+    GRIT_CUDA(launch_restore(ctx->geom, ctx->d_tables, im->d_packed, m.n_slots, im->d_ref, im->d_crc, m.n_pages, a, b, im->imgs,
+                             im->d_out, im->verify, ctx->d_cnt, s));
+    ctx->launches++;
+    // the byte window of this chunk
+    const uint64_t c0 = (a - p0) * kPage, c1 = (b - p0) * kPage;
+    const uint64_t w0 = std::max(c0, skip_first), w1 = std::min(c1, skip_first + len_bytes);
+    if (w1 > w0) {
+      const char* src = static_cast<const char*>(im->d_out) + (w0 - c0);
+      if (dst_on_device) {
+        GRIT_CUDA(cudaMemcpyAsync(dst + done_bytes, src, w1 - w0, cudaMemcpyDeviceToDevice, s));
+      } else {
+        GRIT_CUDA(cudaMemcpyAsync(im->h_stage, src, w1 - w0, cudaMemcpyDeviceToHost, s));
+      }
+    }
+    if (int rc = read_counters(ctx, s, err, errlen)) return rc;  // syncs
+    if (ctx->h_cnt->n_bad)
+      return fail(err, errlen, GRIT_ECRC, "%s: %llu page(s) failed CRC-32C or had a bad reference, first page %llu", im->dir.c_str(),
+                  (unsigned long long)ctx->h_cnt->n_bad, (unsigned long long)ctx->h_cnt->first_bad);
+    if (w1 > w0) {
+      if (!dst_on_device) memcpy(dst + done_bytes, im->h_stage, w1 - w0);
+      done_bytes += w1 - w0;
+    }
+    im->pages_served += b - a;
+  }
+  im->reads++;
+  return GRIT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int grit_image_read_pages(grit_image* im, uint64_t page0, uint64_t n_pages, void* dst, int dst_on_device, char* err,
+                          size_t errlen) {
+  if (!im || (n_pages && !dst)) return fail(err, errlen, GRIT_EINVAL, "null argument");
+  if (page0 > im->m.n_pages || n_pages > im->m.n_pages - page0)
+    return fail(err, errlen, GRIT_EINVAL, "pages %llu..%llu are outside the image (%llu pages)", (unsigned long long)page0,
+                (unsigned long long)(page0 + n_pages), (unsigned long long)im->m.n_pages);
+  return image_read_pages(im, page0, page0 + n_pages, static_cast<char*>(dst), dst_on_device != 0, 0, n_pages * kPage, err, errlen);
+}
+
+int grit_image_stat(grit_image* im, const char* relpath, uint64_t* size, uint32_t* mode, uint64_t* first_page, char* err,
+                    size_t errlen) {
+  if (!im || !relpath) return fail(err, errlen, GRIT_EINVAL, "null argument");
+  for (const auto& e : im->m.entries)
+    if (e.path == relpath) {
+      if (size) *size = e.size;
+      if (mode) *mode = e.mode | (e.type == 0 ? 040000u : 0100000u);
+      if (first_page) *first_page = e.first_page;
+      return GRIT_OK;
+    }
+  return fail(err, errlen, GRIT_EIO, "%s: no such file in the image", relpath);
+}
+
+int64_t grit_image_read(grit_image* im, const char* relpath, uint64_t offset, uint64_t len, void* h_dst, char* err,
+                        size_t errlen) {
+  if (!im || !relpath || (len && !h_dst)) return fail(err, errlen, GRIT_EINVAL, "null argument");
+  for (const auto& e : im->m.entries)
+    if (e.type == 1 && e.path == relpath) {
+      if (offset >= e.size) return 0;  // like pread(2) at or past the end
+      len = std::min(len, e.size - offset);
+      const uint64_t p0 = e.first_page + offset / kPage, p1 = e.first_page + (offset + len + kPage - 1) / kPage;
+      if (int rc = image_read_pages(im, p0, p1, static_cast<char*>(h_dst), false, offset % kPage, len, err, errlen)) return rc;
+      return (int64_t)len;
+    }
+  return fail(err, errlen, GRIT_EIO, "%s: no such file in the image", relpath);
+}
+
+uint64_t grit_image_resident_slots(grit_image* im) {
+  if (!im) return 0;
+  std::lock_guard<std::mutex> l(im->mu);
+  return im->slots_resident;
 }
 
 }  // extern "C"

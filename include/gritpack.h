@@ -380,6 +380,36 @@ int grit_verify_dir(const char *src_dir, const grit_opts *opts,
 int grit_image_deps(const char *dir, int recursive, char *out, size_t outlen,
                     size_t *needed, char *err, size_t errlen);
 
+/* ---- a packed checkpoint served page by page -----------------
+ * The reference restores the whole tree to local disk before the runtime may
+ * start (restore.go:16-20; patched containerd waits for the sentinel,
+ * contrib/containerd/grit-interceptor.diff:146-165) and CRIU then reads it all
+ * again (cmd/containerd-shim-grit-v1/process/init_state.go:163).  A grit_image
+ * keeps the packed checkpoint open instead: grit_image_open returns once the
+ * metadata and the images it refers to (parent, lower ranks) are in place and
+ * streams the stored pages into HBM in the background; a read waits only for
+ * the slots it needs, restores and CRC-checks the pages on the GPU and hands
+ * them over -- to host memory (a lazy-pages server answering CRIU's faults, a
+ * FUSE view of the tree) or to device memory (device state that need not touch
+ * the host again).  opts: device, verify, io_threads.  Reads are serialised. */
+typedef struct grit_image grit_image;
+int grit_image_open(const char *packed_dir, const grit_opts *opts,
+                    grit_image **out, char *err, size_t errlen);
+void grit_image_close(grit_image *img);
+/* size, mode (with the file-type bits) and first stream page of a path of the tree */
+int grit_image_stat(grit_image *img, const char *relpath, uint64_t *size,
+                    uint32_t *mode, uint64_t *first_page, char *err, size_t errlen);
+/* pread on a file of the tree: returns the bytes delivered (0 at or past the
+ * end) or a negative GRIT_E* code. */
+int64_t grit_image_read(grit_image *img, const char *relpath, uint64_t offset,
+                        uint64_t len, void *h_dst, char *err, size_t errlen);
+/* pages [page0, page0 + n_pages) of the page stream into host memory, or with
+ * dst_on_device into memory of the image's GPU. */
+int grit_image_read_pages(grit_image *img, uint64_t page0, uint64_t n_pages,
+                          void *dst, int dst_on_device, char *err, size_t errlen);
+/* how many stored pages have reached the GPU so far (n_slots when all have) */
+uint64_t grit_image_resident_slots(grit_image *img);
+
 /* ---- CRIU-aware ingest ---------------------------------------
  * The tree the agent uploads is a CRIU image directory written at
  * pkg/gritagent/checkpoint/runtime.go:122-134; the reference copies it as
