@@ -31,7 +31,7 @@ int ensure_table(grit_ctx* ctx, uint64_t n_items, DedupTable* t, char* err, size
 }
 
 int ensure_status(grit_ctx* ctx, uint64_t n_pages, char* err, size_t errlen) {
-  const uint64_t tile = std::min<uint64_t>(kCompactTile, fused_tile_pages());
+  const uint64_t tile = std::min<uint64_t>(kCompactTile, onepass_tile_pages());
   const uint64_t tiles = (n_pages + tile - 1) / tile + 1;
   if (tiles > ctx->status_cap) {
     if (ctx->d_status) cudaFree(ctx->d_status);
@@ -64,9 +64,6 @@ bool write_through_pack() {
   return v;
 }
 
-// The pack runs K1, K2, K3 as three kernels (DRAM traffic N + 2U).  GRITPACK_FUSED=1 selects the
-// experimental single-pass kernel (k_pack_fused, N + U when its re-reads hit L2); on B200 it is
-// currently slower, so it is opt-in.
 int ctx_dev(grit_ctx* ctx, int id, size_t bytes, void** out, char* err, size_t errlen) {
   grit_ctx::Buf& b = ctx->dev[id];
   if (bytes > b.cap) {
@@ -93,10 +90,12 @@ int ctx_pin(grit_ctx* ctx, int id, size_t bytes, void** out, char* err, size_t e
   return GRIT_OK;
 }
 
-bool staged_pack() {
+// How grit_pack_buffer packs an image that the sample did not find dense: GRITPACK_ONEPASS=0 keeps the three
+// kernels K1, K2, K3 (DRAM traffic N + 2U); otherwise the single-pass kernel (k_pack_onepass, N + U) runs.
+bool onepass_pack() {
   static const bool v = [] {
-    const char* e = getenv("GRITPACK_FUSED");
-    return !(e && *e && *e != '0');
+    const char* e = getenv("GRITPACK_ONEPASS");
+    return !(e && *e == '0');
   }();
   return v;
 }
@@ -377,17 +376,40 @@ int grit_pack_buffer(grit_ctx* ctx, const void* d_image, uint64_t n_pages, const
   cudaStream_t s = pick(ctx, stream);
   if (int rc = reset_counters(ctx, s, err, errlen)) return rc;
   GRIT_CUDA(cudaEventRecord(ctx->ev0, s));
+  // Three ways to pack, chosen per image:
+  //   through  a full image whose sample looks dense (weights, optimizer state): K1 stores every page to its own slot
+  //            while analysing it and K3 finds the pages in place -- N read + N written;
+  //   onepass  everything else: one kernel, pages parked in TMEM until their verdict -- N read + U written;
+  //   staged   K1, K2, K3 as separate kernels -- N + 2U (GRITPACK_ONEPASS=0, and the streamed host pipelines).
+  enum { kStaged, kThrough, kOnepass } path = kStaged;
+  const bool full = !(parent && parent->n_pages) && n_peers == 0;
   bool staged = false;
-  if (staged_pack()) {  // K1, K2, K3 as separate kernels
-    // A full (not incremental, single-rank) image may be dense -- weights, optimizer state: no zero pages,
-    // no duplicates -- and then compaction is the identity: K1 writes such pages through to their own
-    // slot and K3 finds them in place.  A sample of the image decides, on the device.
-    const bool try_through = n_pages && !(parent && parent->n_pages) && n_peers == 0 && d_packed && write_through_pack();
-    if (try_through) {
+  ctx->through_image = nullptr;
+  if (n_pages && d_packed) {
+    if (full && write_through_pack()) {  // the sample decides on the device; the host needs the answer to pick kernels
+      GRIT_CUDA(launch_probe_dense(d_image, n_pages, ctx->d_cnt, s));
+      ctx->launches++;
+      GRIT_CUDA(cudaMemcpyAsync(&ctx->h_cnt->dense_hint, &ctx->d_cnt->dense_hint, sizeof(unsigned int), cudaMemcpyDeviceToHost, s));
+      GRIT_CUDA(cudaStreamSynchronize(s));
+      if (ctx->h_cnt->dense_hint) path = kThrough;
+    }
+    if (path != kThrough && onepass_pack()) path = kOnepass;
+  }
+  if (path == kOnepass) {
+    DedupTable t{};
+    PeerCrcs crcs{};
+    if (int rc = dedup_async(ctx, n_pages, d_crc, d_hash, d_ref, parent, peers, n_peers, s, err, errlen, &t, &crcs)) return rc;
+    if (int rc = ensure_status(ctx, n_pages, err, errlen)) return rc;
+    const uint64_t tiles = (n_pages + onepass_tile_pages() - 1) / onepass_tile_pages();
+    GRIT_CUDA(cudaMemsetAsync(ctx->d_status, 0, tiles * sizeof(unsigned long long), s));
+    GRIT_CUDA(launch_pack_onepass(ctx->geom, ctx->d_tables, d_image, n_pages, d_crc, d_hash, d_ref, t, crcs, d_packed,
+                                  capacity_pages, ctx->d_status, ctx->d_cnt, s));
+    ctx->launches++;
+  } else {
+    if (path == kThrough) {
       if (int rc = analyze_through_async(ctx, d_image, n_pages, d_crc, d_hash, d_ref, d_packed, capacity_pages, s, err, errlen))
         return rc;
     } else {
-      ctx->through_image = nullptr;
       GRIT_CUDA(launch_analyze(ctx->geom, ctx->d_tables, d_image, n_pages, d_crc, d_hash, d_ref, s));
       ctx->launches++;
     }
@@ -396,16 +418,6 @@ int grit_pack_buffer(grit_ctx* ctx, const void* d_image, uint64_t n_pages, const
     GRIT_CUDA(cudaEventRecord(ctx->evB, s));
     staged = true;
     if (int rc = compact_async(ctx, d_image, n_pages, d_ref, d_packed, capacity_pages, 0, s, err, errlen)) return rc;
-  } else if (n_pages) {
-    DedupTable t{};
-    PeerCrcs crcs{};
-    if (int rc = dedup_async(ctx, n_pages, d_crc, d_hash, d_ref, parent, peers, n_peers, s, err, errlen, &t, &crcs)) return rc;
-    if (int rc = ensure_status(ctx, n_pages, err, errlen)) return rc;
-    const uint64_t tiles = (n_pages + fused_tile_pages() - 1) / fused_tile_pages();
-    GRIT_CUDA(cudaMemsetAsync(ctx->d_status, 0, tiles * sizeof(unsigned long long), s));
-    GRIT_CUDA(launch_pack_fused(ctx->geom, ctx->d_tables, d_image, n_pages, 0, d_crc, d_hash, d_ref, t, crcs, d_packed,
-                                capacity_pages, 0, false, ctx->d_status, ctx->d_cnt, s));
-    ctx->launches++;
   }
   GRIT_CUDA(cudaEventRecord(ctx->ev1, s));
   if (int rc = read_counters(ctx, s, err, errlen)) return rc;
@@ -429,8 +441,7 @@ int grit_pack_buffer(grit_ctx* ctx, const void* d_image, uint64_t n_pages, const
       cudaEventElapsedTime(&ms, ctx->evB, ctx->ev1);
       stats->stage_ms[2] = ms;
     }
-    stats->wrote_through = staged && n_pages && !(parent && parent->n_pages) && n_peers == 0 && d_packed &&
-                           write_through_pack() && c.dense_hint;
+    stats->wrote_through = path == kThrough ? 1 : (path == kOnepass ? 2 : 0);
   }
   if (c.overflow)
     return fail(err, errlen, GRIT_EINVAL, "packed buffer too small: %llu pages did not fit capacity %llu",

@@ -151,21 +151,14 @@ int PackStream::submit(uint64_t i, const void* h_src, uint64_t n_pages, char* er
     GRIT_CUDA(cudaEventRecord(ctx_->ev0, s));
     timing_started_ = true;
   }
-  const uint64_t tile = staged_pack() ? kCompactTile : fused_tile_pages();
-  GRIT_CUDA(cudaMemsetAsync(ctx_->d_status, 0, (n_pages + tile - 1) / tile * sizeof(unsigned long long), s));
-  GRIT_CUDA(cudaMemsetAsync(&ctx_->d_cnt->ticket, 0, 3 * sizeof(unsigned int), s));  // ticket, copy_ticket, watermark
-  if (staged_pack()) {
-    GRIT_CUDA(launch_analyze(ctx_->geom, ctx_->d_tables, d_in_[b], n_pages, d_crc_ + p0, d_hash_ + p0, d_ref_ + p0, s));
-    GRIT_CUDA(launch_table_insert(ctx_->geom, table_, d_hash_ + p0, d_ref_ + p0, n_pages, kOriginSelf, p0, s));
-    GRIT_CUDA(launch_resolve(ctx_->geom, table_, p0, p0 + n_pages, d_crc_, d_hash_, d_ref_, crcs_, s));
-    GRIT_CUDA(launch_compact(ctx_->geom, d_in_[b], n_pages, d_ref_ + p0, d_out_[b], chunk_pages_, 0, true,
-                             ctx_->d_status, ctx_->d_cnt, s));
-    ctx_->launches += 4;
-  } else {
-    GRIT_CUDA(launch_pack_fused(ctx_->geom, ctx_->d_tables, d_in_[b], n_pages, p0, d_crc_, d_hash_, d_ref_, table_, crcs_,
-                                d_out_[b], chunk_pages_, 0, true, ctx_->d_status, ctx_->d_cnt, s));
-    ctx_->launches++;
-  }
+  GRIT_CUDA(cudaMemsetAsync(ctx_->d_status, 0, (n_pages + kCompactTile - 1) / kCompactTile * sizeof(unsigned long long), s));
+  GRIT_CUDA(cudaMemsetAsync(&ctx_->d_cnt->ticket, 0, 3 * sizeof(unsigned int), s));  // ticket and its neighbours
+  GRIT_CUDA(launch_analyze(ctx_->geom, ctx_->d_tables, d_in_[b], n_pages, d_crc_ + p0, d_hash_ + p0, d_ref_ + p0, s));
+  GRIT_CUDA(launch_table_insert(ctx_->geom, table_, d_hash_ + p0, d_ref_ + p0, n_pages, kOriginSelf, p0, s));
+  GRIT_CUDA(launch_resolve(ctx_->geom, table_, p0, p0 + n_pages, d_crc_, d_hash_, d_ref_, crcs_, s));
+  GRIT_CUDA(launch_compact(ctx_->geom, d_in_[b], n_pages, d_ref_ + p0, d_out_[b], chunk_pages_, 0, true,
+                           ctx_->d_status, ctx_->d_cnt, s));
+  ctx_->launches += 4;
   GRIT_CUDA(cudaMemcpyAsync(&h_counts_[b], &ctx_->d_cnt->n_stored, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
   // the chunk's per-page arrays are final now: bring them to pinned staging (u32 ref | u32 crc | u64 hash)
   char* meta = static_cast<char*>(h_meta_[b]);

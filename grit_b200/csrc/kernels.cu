@@ -73,32 +73,6 @@ __device__ __forceinline__ void stg_stream(uint4* p, const uint4& v) {
                : "memory");
 }
 
-// L2 eviction policies (descriptor constants after compilation).  The fused pack reads every tile
-// twice: the first read asks L2 to keep the lines (evict_last), the second read and all streamed
-// writes mark theirs evict_first, so the tiles in flight, not the data already done with, own L2.
-__device__ __forceinline__ uint64_t policy_evict_last() {
-  uint64_t p;
-  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
-  return p;
-}
-__device__ __forceinline__ uint64_t policy_evict_first() {
-  uint64_t p;
-  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
-  return p;
-}
-__device__ __forceinline__ uint4 ldg_hint(const uint4* p, uint64_t pol) {
-  uint4 v;
-  asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
-               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
-               : "l"(p), "l"(pol));
-  return v;
-}
-__device__ __forceinline__ void stg_hint(uint4* p, const uint4& v, uint64_t pol) {
-  asm volatile("st.global.L1::no_allocate.L2::cache_hint.v4.u32 [%0], {%1,%2,%3,%4}, %5;" ::"l"(p), "r"(v.x),
-               "r"(v.y), "r"(v.z), "r"(v.w), "l"(pol)
-               : "memory");
-}
-
 __device__ __forceinline__ uint32_t lds32(uint32_t byte_off) {
   return *reinterpret_cast<const uint32_t*>(smem + byte_off);
 }
@@ -175,9 +149,9 @@ __device__ __forceinline__ void static_for(F&& f) {
 constexpr int kRing = 16;  // 16-byte loads each lane keeps in flight (half a page per 8-lane group)
 
 template <bool kHint>
-__device__ __forceinline__ uint4 ldg_or_zero(const uint4* p, bool on, uint64_t pol) {
+__device__ __forceinline__ uint4 ldg_or_zero(const uint4* p, bool on, uint64_t) {
   if (!on) return make_uint4(0, 0, 0, 0);
-  return kHint ? ldg_hint(p, pol) : ldg_stream(p);
+  return ldg_stream(p);
 }
 
 template <bool kHint = false, int KR>
@@ -653,200 +627,215 @@ k_compact(const uint4* __restrict__ image, uint64_t n_pages, uint32_t* __restric
   }
 }
 
-// ------------------------------------------------------------------ K1+K2+K3 fused
-// One pass over the image with two kinds of jobs on 128-page tiles, handed to whichever CTA is
-// free (persistent grid, one CTA per SM):
-//   ANALYZE(t)  K1 on tile t (HBM -> registers), crc/hash written, non-zero hashes entered in the
-//               table, the page's table slot parked in ref[]; then status[t] = INSERTED.
-//   COPY(c)     only taken once every tile <= c is INSERTED (so the table's minimum for each of
-//               c's hashes is final) and in tile order: decide the references, publish the count
-//               of pages to store, decoupled look-back over earlier COPY jobs for the first slot,
-//               copy the stored pages into the packed image.  The tile was analysed microseconds
-//               ago, so these reads should hit L2 and DRAM sees the image once (N read + U written).
-// COPY has priority, so the distance between a tile's two reads stays short.  No job ever waits for
-// a job that is not already running: ANALYZE waits for nothing, COPY(c) looks back at COPY jobs
-// claimed before it.  CTAs without a job poll.
-constexpr int kFusedRounds = 2;
-constexpr int kFusedTile = kWarps * 4 * kFusedRounds;  // 128 pages = 512 KiB
+// ------------------------------------------------------------------ K1+K2+K3 in one pass, pages parked in TMEM
+// The two-pass pack reads every stored page twice (K1, then K3): N + 2U of DRAM traffic for N + U of work.  Here a
+// page is read once, and while its CRC / hash64 are computed its 16-byte values are parked in tensor memory -- the
+// 256 KiB per SM that only tcgen05 instructions reach and that nothing else in this library uses (the lane-private
+// CRC tables leave no room in shared memory).  Once the page's fate is known it is written out of TMEM to its slot,
+// or dropped.  DRAM sees N read + U written.
+//
+// A CTA (one per SM) owns tiles t = k * gridDim + blockIdx of 32 pages.  Eight compute warps analyse a tile exactly
+// like k_analyze (8 lanes per page, 4 pages per warp) and store every value they consume to their TMEM lanes
+// (tcgen05.st 32x32b.x4: thread i -> its quadrant's lane i, four columns per step); two TMEM halves alternate, so
+// tile k+1 is analysed while tile k waits for its verdict.  Two control warps (even / odd tiles) do everything that
+// needs the rest of the GPU, off the compute warps' critical path:
+//   insert the tile's hashes in the table, publish INSERTED;
+//   wait until every earlier tile has inserted (the owner of a hash is the lowest page holding it, so a verdict
+//   needs all earlier pages in the table), then read each page's owner: keep / DUP / PARENT / PEER;
+//   publish the tile's count of kept pages, decoupled look-back over the earlier tiles for the first slot;
+//   hand the 32 slots (or "drop") to the compute warps, which move their pages TMEM -> registers -> packed image
+//   (tcgen05.ld + 128-bit stores) before they reuse the half.
+// Every wait is for a lower-numbered tile, every CTA is resident, each takes its tiles in increasing order: the
+// lowest unfinished tile can always proceed.
+constexpr int kOpWarps = 8;                       // compute warps
+constexpr int kOpThreads = (kOpWarps + 2) * 32;   // + two control warps
+constexpr int kOpTile = kOpWarps * 4;             // 32 pages, one per control lane
 constexpr unsigned long long kStInserted = 1ull << 62, kStAgg = 2ull << 62, kStPrefix = 3ull << 62;
-constexpr uint32_t kJobAnalyze = 0, kJobCopy = 1, kJobRetry = 2, kJobExit = 3;
-constexpr uint32_t kNoTile = 0xFFFFFFFFu;
-constexpr uint32_t kMaxLead = 192;  // ANALYZE may run at most this many tiles ahead of COPY (L2 residency)
+constexpr int kBarComputed = 1, kBarDecided = 3;  // named barriers: + half
+constexpr int kOpSlotDrop = -1;
 
-__device__ __forceinline__ uint32_t ld_cg_u32(const uint32_t* p) { return __ldcg(p); }
-__device__ __forceinline__ uint32_t ld_relaxed_u32(const unsigned int* p) {
-  uint32_t v;
-  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+__device__ __forceinline__ void bar_sync(int id, int count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
+__device__ __forceinline__ void bar_arrive(int id, int count) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory"); }
+
+__device__ __forceinline__ void tmem_st4(uint32_t taddr, const uint4& v) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};" ::"r"(taddr), "r"(v.x), "r"(v.y), "r"(v.z),
+               "r"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ uint4 tmem_ld4(uint32_t taddr) {
+  uint4 v;
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "r"(taddr)
+               : "memory");
   return v;
 }
+__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
-__global__ void __launch_bounds__(kThreads, 1)
-k_pack_fused(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ image, uint64_t n_pages, uint64_t page0,
-             uint32_t* __restrict__ crc, unsigned long long* __restrict__ hash, uint32_t* __restrict__ ref,
-             DedupTable t, PeerCrcs crcs, uint4* __restrict__ packed, uint64_t capacity_pages, uint64_t slot_base,
-             int chained, unsigned long long* __restrict__ status, DevCounters* __restrict__ cnt) {
-  __shared__ uint32_t s_job, s_tile, s_excl, s_warp_cnt[4];
-  __shared__ uint16_t s_list[kFusedTile];
-  load_tables(tabs);
+struct OnepassShared {
+  uint32_t tmem_base;
+  unsigned long long hash[2][kOpTile];
+  uint32_t crc[2][kOpTile];
+  uint32_t nonzero[2][kOpTile];  // 1: page exists and is not all zero; 0: zero page; 2: no such page
+  int slot[2][kOpTile];          // verdict: slot in the packed image, or kOpSlotDrop
+};
+
+__global__ void __launch_bounds__(kOpThreads, 1)
+k_pack_onepass(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ image, uint64_t n_pages,
+               uint32_t* __restrict__ crc, unsigned long long* __restrict__ hash, uint32_t* __restrict__ ref, DedupTable t,
+               PeerCrcs crcs, uint4* __restrict__ packed, uint64_t capacity_pages, unsigned long long* __restrict__ status,
+               DevCounters* __restrict__ cnt) {
+  __shared__ OnepassShared sh;
   const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const uint32_t g = lane >> 3, l = lane & 7, lane4 = lane * 4;
-  const uint32_t n_tiles = (uint32_t)((n_pages + kFusedTile - 1) / kFusedTile);
-  const uint64_t ref_base = chained ? cnt->slot_base : slot_base;
-  const uint64_t out_base = chained ? 0 : slot_base;
-  const uint64_t keep_in_l2 = policy_evict_last(), done_with = policy_evict_first();
-  uint32_t n_kind[5] = {0, 0, 0, 0, 0};  // this thread's page counts per kind
-  uint32_t pending = kNoTile;             // warp 0: a COPY ticket taken before its tile was ready
+  const uint32_t n_tiles = (uint32_t)((n_pages + kOpTile - 1) / kOpTile);
+  if (blockIdx.x >= n_tiles) return;
+  const uint32_t my_tiles = (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x;  // tiles k = 0 .. my_tiles-1
+  load_tables(tabs);  // all warps fill the tables; ends with __syncthreads
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(
+                     (uint32_t)__cvta_generic_to_shared(&sh.tmem_base))
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = sh.tmem_base;
 
-  for (;;) {
-    // ---- pick a job (warp 0): a COPY if one is ready, else an ANALYZE.  COPY tickets are taken with
-    // an atomicAdd as soon as some tile is ready; a ticket that overshoots the watermark is kept
-    // (`pending`) and this CTA analyses other tiles until its tile is ready.
-    if (warp == 0) {
-      uint32_t job = kJobRetry, tile = 0;
-      uint32_t w = ld_relaxed_u32(&cnt->watermark);
-      for (;;) {  // advance the watermark over every tile that has published INSERTED
-        const uint32_t idx = w + lane;
-        const bool ins = idx < n_tiles && (ld_status(&status[idx]) >> 62) != 0;
-        const uint32_t nb = ~__ballot_sync(0xFFFFFFFFu, ins);
-        const uint32_t run = nb ? (uint32_t)__ffs(nb) - 1u : 32u;  // leading INSERTED tiles, 0..32
-        w += run;
-        if (run < 32) break;
-      }
-      if (lane == 0) atomicMax(&cnt->watermark, w);
-      uint32_t c = ld_relaxed_u32(&cnt->copy_ticket);
-      if (pending == kNoTile && c < n_tiles && c < w) {
-        uint32_t tk = 0;
-        if (lane == 0) tk = atomicAdd(&cnt->copy_ticket, 1u);
-        tk = __shfl_sync(0xFFFFFFFFu, tk, 0);
-        if (tk < n_tiles) pending = tk;
-        c = tk + 1;
-      }
-      if (pending != kNoTile && pending < w) {
-        job = kJobCopy;
-        tile = pending;
-        pending = kNoTile;
-      } else {
-        const uint32_t a = ld_relaxed_u32(&cnt->ticket);
-        if (a < n_tiles) {
-          if (a < c + kMaxLead) {
-            uint32_t tk = 0;
-            if (lane == 0) tk = atomicAdd(&cnt->ticket, 1u);
-            tk = __shfl_sync(0xFFFFFFFFu, tk, 0);
-            if (tk < n_tiles) {
-              job = kJobAnalyze;
-              tile = tk;
-            }
-          }
-        } else if (pending == kNoTile && c >= n_tiles) {
-          job = kJobExit;
-        }
-      }
-      if (lane == 0) {
-        s_job = job;
-        s_tile = tile;
-      }
-    }
-    __syncthreads();
-    const uint32_t job = s_job, tile = s_tile;
-    __syncthreads();  // s_job / s_tile may be rewritten as soon as every thread has read them
-    if (job == kJobExit) break;
-    if (job == kJobRetry) {
-      __nanosleep(200);
-      continue;
-    }
-    const uint64_t base = (uint64_t)tile * kFusedTile;  // first page of the tile, chunk-local
-
-    if (job == kJobAnalyze) {
-      uint4 ring[kRing];
-      uint64_t p = base + warp * 4 + g;
-      const uint4* src = image + p * 256 + l;
-      ring_fill<true>(ring, src, p < n_pages, keep_in_l2);
+  if (warp < kOpWarps) {
+    // ---------------------------------------------------------------- compute warps
+    const uint32_t g = lane >> 3, l = lane & 7, lane4 = lane * 4;
+    // this warp's TMEM window: its quadrant's 32 lanes, 256 columns (two halves of 128) at (warp / 4) * 256
+    const uint32_t tm = tmem_base + (((warp & 3) * 32) << 16) + (warp >> 2) * 256;
+    auto drain = [&](uint32_t half) {  // the warp's four pages of that half: TMEM -> their slots
+      const int s = sh.slot[half][warp * 4 + g];
+      uint4* d = packed + (uint64_t)(s < 0 ? 0 : s) * 256 + l;
+      const bool any = __any_sync(0xFFFFFFFFu, s >= 0);
+      if (any) {
 #pragma unroll 1
-      for (int r = 0; r < kFusedRounds; r++) {
-        PageAcc a;
-        a.z = 0;
-        a.h = 0;
-        const bool on = p < n_pages;
-        const uint64_t p_next = p + kWarps * 4;
-        const uint4* src_next = image + p_next * 256 + l;
-        const bool next_on = (r + 1 < kFusedRounds) && p_next < n_pages;
-        page_pass<true, true, true>(a, ring, src, on, src_next, next_on, lane4, [](auto, const uint4&) {}, keep_in_l2);
-        const uint32_t page_crc = finish_crc(a, l);
-        uint32_t z = a.z;
-        z |= __shfl_xor_sync(0xFFFFFFFFu, z, 1);
-        z |= __shfl_xor_sync(0xFFFFFFFFu, z, 2);
-        z |= __shfl_xor_sync(0xFFFFFFFFu, z, 4);
-        const unsigned long long h = finish_hash(a, l);
-        if (l == 0 && on) {
-          const uint64_t gp = page0 + p;
-          crc[gp] = page_crc;
-          hash[gp] = h;
-          uint32_t parked = 0u;  // zero page
-          if (z) {
-            const uint32_t v = kOriginSelf << 26 | (uint32_t)gp;
-            uint64_t sl = table_home(h, t.mask);
-            for (;; sl = (sl + 1) & t.mask) {
-              unsigned long long k = t.keys[sl];
-              if (k == 0ull) k = atomicCAS(&t.keys[sl], 0ull, h);
-              if (k == 0ull || k == h) {
-                atomicMin(&t.vals[sl], v);
-                break;
-              }
-            }
-            parked = 0x80000000u | (uint32_t)sl;  // the page's table slot, for the COPY job
+        for (int jb = 0; jb < 32; jb += 8) {  // eight steps per round trip to TMEM, then their eight stores
+          uint4 v[8];
+#pragma unroll
+          for (int j = 0; j < 8; j++) v[j] = tmem_ld4(tm + half * 128 + 4 * (jb + j));
+          tmem_wait_ld();
+          if (s >= 0) {
+#pragma unroll
+            for (int j = 0; j < 8; j++) stg_stream(d + 8 * (jb + j), v[j]);
           }
-          ref[gp] = parked;
         }
-        p = p_next;
-        src = src_next;
       }
-      __threadfence();  // crc / hash / ref stores and table atomics before the flag
-      __syncthreads();
-      if (threadIdx.x == 0) st_status(&status[tile], kStInserted);
-      continue;
+    };
+    uint4 ring[kRing];
+    uint64_t p = ((uint64_t)blockIdx.x * kOpTile) + warp * 4 + g;
+    const uint4* src = image + p * 256 + l;
+    ring_fill(ring, src, p < n_pages);
+    for (uint32_t k = 0; k < my_tiles; k++) {
+      const uint32_t half = k & 1;
+      PageAcc a;
+      a.z = 0;
+      a.h = 0;
+      const bool on = p < n_pages;
+      const uint64_t p_next = p + (uint64_t)gridDim.x * kOpTile;
+      const uint4* src_next = image + p_next * 256 + l;
+      const bool next_on = k + 1 < my_tiles && p_next < n_pages;
+      const uint32_t tcol = tm + half * 128;
+      page_pass<true, true>(a, ring, src, on, src_next, next_on, lane4, [&](auto jc, const uint4& v) {
+        constexpr int j = decltype(jc)::value;
+        tmem_st4(tcol + 4 * j, v);
+      });
+      const uint32_t page_crc = finish_crc(a, l);
+      uint32_t z = a.z;
+      z |= __shfl_xor_sync(0xFFFFFFFFu, z, 1);
+      z |= __shfl_xor_sync(0xFFFFFFFFu, z, 2);
+      z |= __shfl_xor_sync(0xFFFFFFFFu, z, 4);
+      const unsigned long long page_hash = finish_hash(a, l);
+      if (l == 0) {
+        const uint32_t pl = warp * 4 + g;
+        sh.hash[half][pl] = page_hash;
+        sh.crc[half][pl] = page_crc;
+        sh.nonzero[half][pl] = on ? (z ? 1u : 0u) : 2u;
+        if (on) {
+          crc[p] = page_crc;
+          hash[p] = page_hash;
+        }
+      }
+      tmem_wait_st();
+      __threadfence_block();
+      bar_arrive(kBarComputed + half, kOpWarps * 32 + 32);  // the control warp of this parity takes it from here
+      if (k >= 1) {  // the previous tile's verdict has had a whole tile's time to arrive
+        bar_sync(kBarDecided + (half ^ 1), kOpWarps * 32 + 32);
+        drain(half ^ 1);
+      }
+      p = p_next;
+      src = src_next;
     }
-
-    // ---- COPY(tile): every tile <= tile has inserted
-    __threadfence();
-    const uint32_t lp = threadIdx.x;
-    uint32_t kind = 7u;  // 7 = no page
-    bool keep = false;
-    uint64_t gp = page0 + base + lp;
-    if (lp < (uint32_t)kFusedTile && base + lp < n_pages) {
-      const uint32_t parked = ld_cg_u32(&ref[gp]);
-      if (parked == 0u) {
-        kind = 0u;
-      } else {
-        const uint32_t ts = parked & 0x7FFFFFFFu;
-        const uint32_t v = ld_cg_u32(&t.vals[ts]), origin = v >> 26, idx = v & ((1u << 26) - 1);
-        uint32_t out = kRefKeep;
-        if (!(origin == kOriginSelf && idx == (uint32_t)gp)) {
-          const uint32_t mine = ld_cg_u32(&crc[gp]);
+    const uint32_t last = (my_tiles - 1) & 1;
+    bar_sync(kBarDecided + last, kOpWarps * 32 + 32);
+    drain(last);
+  } else {
+    // ---------------------------------------------------------------- control warps: lane i <-> page i of the tile
+    const uint32_t half = warp - kOpWarps;  // control warp 0: even tiles (TMEM half 0), control warp 1: odd tiles
+    const uint32_t lt_mask = (1u << lane) - 1;
+    uint32_t n_kind[5] = {0, 0, 0, 0, 0};
+    uint32_t wm = 0;  // every tile below wm is known to have inserted
+    for (uint32_t k = half; k < my_tiles; k += 2) {
+      const uint32_t tile = k * gridDim.x + blockIdx.x;
+      const uint64_t p = (uint64_t)tile * kOpTile + lane;
+      bar_sync(kBarComputed + half, kOpWarps * 32 + 32);
+      const uint32_t nz = sh.nonzero[half][lane];
+      const unsigned long long h = sh.hash[half][lane];
+      const uint32_t my_crc = sh.crc[half][lane];
+      uint64_t sl = 0;
+      if (nz == 1u) {
+        const uint32_t v = kOriginSelf << 26 | (uint32_t)p;
+        for (sl = table_home(h, t.mask);; sl = (sl + 1) & t.mask) {
+          unsigned long long key = t.keys[sl];
+          if (key == 0ull) key = atomicCAS(&t.keys[sl], 0ull, h);
+          if (key == 0ull || key == h) {
+            if (key == 0ull || __ldcg(&t.vals[sl]) > v) atomicMin(&t.vals[sl], v);
+            break;
+          }
+        }
+      }
+      __threadfence();  // the tile's crc / hash stores (seen through the barrier) and table atomics before the flag
+      __syncwarp();
+      if (lane == 0) st_status(&status[tile], kStInserted);
+      // every earlier tile must have inserted before an owner can be read
+      for (uint32_t b0 = wm; b0 < tile; b0 += 128) {
+        for (;;) {
+          unsigned long long s0 = kStInserted, s1 = kStInserted, s2 = kStInserted, s3 = kStInserted;
+          const uint32_t i0 = b0 + lane;
+          if (i0 < tile) s0 = ld_status(&status[i0]);
+          if (i0 + 32 < tile) s1 = ld_status(&status[i0 + 32]);
+          if (i0 + 64 < tile) s2 = ld_status(&status[i0 + 64]);
+          if (i0 + 96 < tile) s3 = ld_status(&status[i0 + 96]);
+          const bool ok = (s0 >> 62) && (s1 >> 62) && (s2 >> 62) && (s3 >> 62);
+          if (__all_sync(0xFFFFFFFFu, ok)) break;
+          __nanosleep(100);
+        }
+      }
+      wm = tile;
+      __threadfence();
+      // verdict
+      uint32_t out = 0u;  // zero page
+      bool keep = false;
+      if (nz == 1u) {
+        const uint32_t v = __ldcg(&t.vals[sl]), origin = v >> 26, idx = v & ((1u << 26) - 1);
+        out = kRefKeep;
+        if (!(origin == kOriginSelf && idx == (uint32_t)p)) {
           const uint32_t ocrc = origin == 0             ? crcs.parent[idx]
-                                : origin == kOriginSelf ? ld_cg_u32(&crc[idx])
+                                : origin == kOriginSelf ? __ldcg(&crc[idx])
                                                         : crcs.peer[origin - 1][idx];
-          if (ocrc == mine)
+          if (ocrc == my_crc)
             out = origin == 0             ? (3u << 29 | idx)
                   : origin == kOriginSelf ? (2u << 29 | idx)
                                           : (4u << 29 | (origin - 1) << 26 | idx);
         }
         keep = out == kRefKeep;
-        kind = keep ? 1u : out >> 29;
-        if (!keep) ref[gp] = out;
       }
-      n_kind[kind]++;
-    }
-    const uint32_t bal = __ballot_sync(0xFFFFFFFFu, keep);
-    if (warp < 4 && lane == 0) s_warp_cnt[warp] = __popc(bal);
-    __syncthreads();
-    uint32_t before = 0, total = 0;
-#pragma unroll
-    for (int w = 0; w < 4; w++) {
-      const uint32_t c = s_warp_cnt[w];
-      before += w < (int)warp ? c : 0u;
-      total += c;
-    }
-    if (warp == 0) {
+      const uint32_t bal = __ballot_sync(0xFFFFFFFFu, keep);
+      const uint32_t total = __popc(bal), rank = __popc(bal & lt_mask);
       if (lane == 0) st_status(&status[tile], (tile == 0 ? kStPrefix : kStAgg) | total);
       uint32_t excl = 0;
       if (tile > 0) {
@@ -854,9 +843,11 @@ k_pack_fused(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ image
         for (;;) {
           const int64_t idx = look - lane;
           unsigned long long st;
-          do {
+          for (;;) {
             st = idx >= 0 ? ld_status(&status[idx]) : kStPrefix;
-          } while (__any_sync(0xFFFFFFFFu, (st >> 62) < 2));
+            if (!__any_sync(0xFFFFFFFFu, (st >> 62) < 2)) break;
+            __nanosleep(40);
+          }
           const uint32_t incl = __ballot_sync(0xFFFFFFFFu, (st >> 62) == 3);
           const uint32_t upto = incl ? (uint32_t)__ffs(incl) - 1u : 31u;
           uint32_t v = lane <= upto ? (uint32_t)st : 0u;
@@ -868,53 +859,36 @@ k_pack_fused(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ image
         }
         if (lane == 0) st_status(&status[tile], kStPrefix | (excl + total));
       }
-      if (lane == 0) {
-        s_excl = excl;
-        if (tile == n_tiles - 1) {
-          cnt->n_stored = excl + total;
-          cnt->slot_base_next = ref_base + excl + total;
-        }
+      if (lane == 0 && tile == n_tiles - 1) {
+        cnt->n_stored = excl + total;
+        cnt->slot_base_next = excl + total;
       }
+      int sv = kOpSlotDrop;
+      if (keep) {
+        const uint32_t slot = excl + rank;
+        out = 1u << 29 | slot;
+        if (slot < capacity_pages) sv = (int)slot;
+        else atomicAdd(&cnt->overflow, 1ull);
+      }
+      if (nz != 2u) {
+        ref[p] = out;
+        n_kind[keep ? 1u : out >> 29]++;
+      }
+      sh.slot[half][lane] = sv;
+      __threadfence_block();
+      bar_arrive(kBarDecided + half, kOpWarps * 32 + 32);
     }
-    const uint32_t rank = before + __popc(bal & ((1u << lane) - 1));
-    if (keep) s_list[rank] = (uint16_t)lp;
-    __syncthreads();
-    const uint64_t first_slot = out_base + s_excl;
-    if (keep) {
-      ref[gp] = 1u << 29 | (uint32_t)(ref_base + s_excl + rank);
-      if (first_slot + rank >= capacity_pages) atomicAdd(&cnt->overflow, 1ull);
+#pragma unroll
+    for (int q = 0; q < 5; q++) {
+      uint32_t v = n_kind[q];
+#pragma unroll
+      for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
+      if (lane == 0 && v) atomicAdd(&cnt->kind[q], (unsigned long long)v);
     }
-    for (uint32_t k = warp; k < total; k += 2 * kWarps) {
-      const uint32_t k2 = k + kWarps;
-      const bool two = k2 < total;
-      const uint64_t sa = first_slot + k, sb = first_slot + k2;
-      const uint4* pa = image + (base + s_list[k]) * 256 + lane;
-      const uint4* pb = image + (base + s_list[two ? k2 : k]) * 256 + lane;
-      uint4 va[8], vb[8];
-#pragma unroll
-      for (int j = 0; j < 8; j++) va[j] = ldg_hint(pa + 32 * j, done_with);
-      if (two) {
-#pragma unroll
-        for (int j = 0; j < 8; j++) vb[j] = ldg_hint(pb + 32 * j, done_with);
-      }
-      if (sa < capacity_pages) {
-#pragma unroll
-        for (int j = 0; j < 8; j++) stg_hint(packed + sa * 256 + lane + 32 * j, va[j], done_with);
-      }
-      if (two && sb < capacity_pages) {
-#pragma unroll
-        for (int j = 0; j < 8; j++) stg_hint(packed + sb * 256 + lane + 32 * j, vb[j], done_with);
-      }
-    }
-    __syncthreads();  // s_list / s_excl / s_warp_cnt are reused by the next COPY job
   }
-#pragma unroll
-  for (int k = 0; k < 5; k++) {
-    uint32_t v = n_kind[k];
-#pragma unroll
-    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
-    if (lane == 0 && v) atomicAdd(&cnt->kind[k], (unsigned long long)v);
-  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
 }
 
 // ------------------------------------------------------------------ K4 restore
@@ -1057,23 +1031,21 @@ cudaError_t configure_kernels() {
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(k_analyze_through, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmBytesWT);
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(k_pack_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmBytes);
+  e = cudaFuncSetAttribute(k_pack_onepass, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmBytes);
   if (e != cudaSuccess) return e;
   return cudaFuncSetAttribute(k_restore, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmBytes);
 }
 
-uint32_t fused_tile_pages() { return kFusedTile; }
+uint32_t onepass_tile_pages() { return kOpTile; }
 
-cudaError_t launch_pack_fused(const LaunchGeom& g, const Gf2Tables* d_tab, const void* d_image, uint64_t n_pages,
-                              uint64_t page0, uint32_t* d_crc, uint64_t* d_hash, uint32_t* d_ref, DedupTable t,
-                              PeerCrcs crcs, void* d_packed, uint64_t capacity_pages, uint64_t slot_base, bool chained,
-                              unsigned long long* d_tile_status, DevCounters* d_cnt, cudaStream_t s) {
+cudaError_t launch_pack_onepass(const LaunchGeom& g, const Gf2Tables* d_tab, const void* d_image, uint64_t n_pages,
+                                uint32_t* d_crc, uint64_t* d_hash, uint32_t* d_ref, DedupTable t, PeerCrcs crcs, void* d_packed,
+                                uint64_t capacity_pages, unsigned long long* d_tile_status, DevCounters* d_cnt, cudaStream_t s) {
   if (!n_pages) return cudaSuccess;
-  const int grid = grid_for(g, n_pages, kFusedTile, 1);
-  k_pack_fused<<<grid, kThreads, kSmBytes, s>>>(d_tab, static_cast<const uint4*>(d_image), n_pages, page0, d_crc,
-                                                reinterpret_cast<unsigned long long*>(d_hash), d_ref, t, crcs,
-                                                static_cast<uint4*>(d_packed), capacity_pages, slot_base,
-                                                chained ? 1 : 0, d_tile_status, d_cnt);
+  const int grid = grid_for(g, n_pages, kOpTile, 1);  // every CTA must be resident: at most one per SM
+  k_pack_onepass<<<grid, kOpThreads, kSmBytes, s>>>(d_tab, static_cast<const uint4*>(d_image), n_pages, d_crc,
+                                                    reinterpret_cast<unsigned long long*>(d_hash), d_ref, t, crcs,
+                                                    static_cast<uint4*>(d_packed), capacity_pages, d_tile_status, d_cnt);
   return cudaGetLastError();
 }
 

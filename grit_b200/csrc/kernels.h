@@ -108,12 +108,12 @@ cudaError_t launch_probe_dense(const void* d_image, uint64_t n_pages, DevCounter
 cudaError_t launch_analyze_auto(const LaunchGeom& g, const Gf2Tables* d_tab, const void* d_image, uint64_t n_pages,
                                 uint32_t* d_crc, uint64_t* d_hash, uint32_t* d_ref, void* d_packed,
                                 uint64_t capacity_pages, uint64_t page_base, DevCounters* d_cnt, cudaStream_t s);
-// K1+K2+K3 in one pass; crc/hash/ref are the whole image's arrays, the chunk starts at page0 of them
-cudaError_t launch_pack_fused(const LaunchGeom& g, const Gf2Tables* d_tab, const void* d_image, uint64_t n_pages,
-                              uint64_t page0, uint32_t* d_crc, uint64_t* d_hash, uint32_t* d_ref, DedupTable t,
-                              PeerCrcs crcs, void* d_packed, uint64_t capacity_pages, uint64_t slot_base, bool chained,
-                              unsigned long long* d_tile_status, DevCounters* d_cnt, cudaStream_t s);
-uint32_t fused_tile_pages();
+// K1+K2+K3 in one pass over a whole device-resident image, pages parked in TMEM between analysis and store.  The
+// table must already hold the parent's and the lower ranks' hashes; d_tile_status: one zeroed word per 32-page tile.
+cudaError_t launch_pack_onepass(const LaunchGeom& g, const Gf2Tables* d_tab, const void* d_image, uint64_t n_pages,
+                                uint32_t* d_crc, uint64_t* d_hash, uint32_t* d_ref, DedupTable t, PeerCrcs crcs, void* d_packed,
+                                uint64_t capacity_pages, unsigned long long* d_tile_status, DevCounters* d_cnt, cudaStream_t s);
+uint32_t onepass_tile_pages();
 cudaError_t launch_restore(const LaunchGeom& g, const Gf2Tables* d_tab, const void* d_packed,
                            uint64_t n_slots, const uint32_t* d_ref, const uint32_t* d_crc,
                            uint64_t n_pages, uint64_t page0, uint64_t page1, PeerImages imgs, void* d_out,
