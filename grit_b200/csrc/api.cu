@@ -90,12 +90,14 @@ int ctx_pin(grit_ctx* ctx, int id, size_t bytes, void** out, char* err, size_t e
   return GRIT_OK;
 }
 
-// How grit_pack_buffer packs an image that the sample did not find dense: GRITPACK_ONEPASS=0 keeps the three
-// kernels K1, K2, K3 (DRAM traffic N + 2U); otherwise the single-pass kernel (k_pack_onepass, N + U) runs.
+// GRITPACK_ONEPASS=1 makes grit_pack_buffer pack every image the sample does not find dense with the single-pass
+// kernel (k_pack_onepass: pages parked in TMEM, N + U of DRAM traffic).  It is bit-exact but on B200 still slower
+// than K1, K2, K3 as separate kernels (N + 2U): the verdict of a tile needs every earlier tile's hashes, and with two
+// tiles of TMEM per SM that chain sits on the critical path (profiles/README.md).  Opt-in until it wins.
 bool onepass_pack() {
   static const bool v = [] {
     const char* e = getenv("GRITPACK_ONEPASS");
-    return !(e && *e == '0');
+    return e && *e && *e != '0';
   }();
   return v;
 }
@@ -379,8 +381,9 @@ int grit_pack_buffer(grit_ctx* ctx, const void* d_image, uint64_t n_pages, const
   // Three ways to pack, chosen per image:
   //   through  a full image whose sample looks dense (weights, optimizer state): K1 stores every page to its own slot
   //            while analysing it and K3 finds the pages in place -- N read + N written;
-  //   onepass  everything else: one kernel, pages parked in TMEM until their verdict -- N read + U written;
-  //   staged   K1, K2, K3 as separate kernels -- N + 2U (GRITPACK_ONEPASS=0, and the streamed host pipelines).
+  //   staged   everything else: K1, K2, K3 as separate kernels -- N + 2U (also the streamed host pipelines);
+  //   onepass  instead of staged with GRITPACK_ONEPASS=1: one kernel, pages parked in TMEM until their verdict --
+  //            N read + U written, but not yet faster (see onepass_pack above).
   enum { kStaged, kThrough, kOnepass } path = kStaged;
   const bool full = !(parent && parent->n_pages) && n_peers == 0;
   bool staged = false;

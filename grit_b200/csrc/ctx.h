@@ -83,6 +83,6 @@ enum DevBuf { kDevIn0 = 0, kDevOut0 = 3, kDevRef = 6, kDevCrc, kDevHash, kDevPar
 enum PinBuf { kPinIn0 = 0, kPinOut0 = 3, kPinCounts = 6, kPinMeta0 = 7, kPinRStageOut0 = 10, kPinRStageIn0 = 13 /* ..15 */,
               kPinRStageOutX0 = 16 /* ..20 */ };
 bool write_through_pack();  // false with GRITPACK_WRITE_THROUGH=0
-bool onepass_pack();  // false with GRITPACK_ONEPASS=0: grit_pack_buffer then never uses the single-pass kernel
+bool onepass_pack();  // true with GRITPACK_ONEPASS=1: grit_pack_buffer packs non-dense images with the single-pass kernel
 
 }  // namespace grit

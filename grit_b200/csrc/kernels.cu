@@ -648,11 +648,25 @@ k_compact(const uint4* __restrict__ image, uint64_t n_pages, uint32_t* __restric
 // Every wait is for a lower-numbered tile, every CTA is resident, each takes its tiles in increasing order: the
 // lowest unfinished tile can always proceed.
 constexpr int kOpWarps = 8;                       // compute warps
-constexpr int kOpThreads = (kOpWarps + 2) * 32;   // + two control warps
+constexpr int kOpDrainWarps = 4;                  // one per TMEM quadrant
+// four warpgroups: compute 0-3 | compute 4-7 | control 8, 9 (10, 11 idle) | drain 12-15; setmaxnreg moves registers
+// from the last two to the first two
+constexpr int kOpThreads = 512;
+constexpr int kOpComputeRegs = 192, kOpOtherRegs = 64;
+constexpr uint32_t kOpNoTile = 0xFFFFFFFFu;
 constexpr int kOpTile = kOpWarps * 4;             // 32 pages, one per control lane
 constexpr unsigned long long kStInserted = 1ull << 62, kStAgg = 2ull << 62, kStPrefix = 3ull << 62;
-constexpr int kBarComputed = 1, kBarDecided = 3;  // named barriers: + half
+constexpr int kBarComputed = 1, kBarDecided = 3, kBarDrained = 5, kBarCompute = 7;  // named barriers: + half
+constexpr int kCntComputed = kOpWarps * 32 + 32, kCntDecided = 32 + kOpDrainWarps * 32, kCntDrained = (kOpDrainWarps + kOpWarps) * 32;
+__device__ __forceinline__ void tmem_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tmem_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 constexpr int kOpSlotDrop = -1;
+#ifndef GRIT_OP_RING
+#define GRIT_OP_RING 8
+#endif
+// 16-byte loads per lane in flight: 8 warps x 32 lanes x 8 x 16 B = 32 KB per SM covers the DRAM latency at this
+// kernel's rate; more only lengthens the queue the control warps' round trips wait in
+constexpr int kOpRing = GRIT_OP_RING;
 
 __device__ __forceinline__ void bar_sync(int id, int count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
 __device__ __forceinline__ void bar_arrive(int id, int count) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory"); }
@@ -673,8 +687,35 @@ __device__ __forceinline__ uint4 tmem_ld4(uint32_t taddr) {
 __device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+#ifdef GRIT_OP_PROF
+__device__ unsigned long long g_op_prof[16];  // ns summed over CTAs: compute, wait verdict, drain | wait computed, insert, wait inserted, verdict, look-back
+__device__ __forceinline__ unsigned long long op_now() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+#define OP_T(var) const unsigned long long var = op_now()
+// a barrier does not block where it is issued but at the first use of what it protects: read the clock after such a use
+__device__ __forceinline__ unsigned long long op_now_after(uint32_t dep) {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t) : "r"(dep));
+  return t;
+}
+#define OP_TD(var, dep) const unsigned long long var = op_now_after((uint32_t)(dep))
+#define OP_ADD(slot, a, b) \
+  if (lane == 0 && (warp == 0 || warp == kOpWarps)) atomicAdd(&g_op_prof[slot], (b) - (a))
+#define OP_ADD_RAW(slot, a, b) atomicAdd(&g_op_prof[slot], (b) - (a))
+#else
+#define OP_T(var)
+#define OP_TD(var, dep)
+#define OP_ADD(slot, a, b)
+#define OP_ADD_RAW(slot, a, b)
+#endif
+
 struct OnepassShared {
   uint32_t tmem_base;
+  uint32_t tile_of_half[2];      // the tile parked in each TMEM half (kOpNoTile: the CTA has run out of tiles)
+  uint32_t next_id;              // hand-over of the next ticket between the compute warps
   unsigned long long hash[2][kOpTile];
   uint32_t crc[2][kOpTile];
   uint32_t nonzero[2][kOpTile];  // 1: page exists and is not all zero; 0: zero page; 2: no such page
@@ -690,7 +731,6 @@ k_pack_onepass(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ ima
   const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const uint32_t n_tiles = (uint32_t)((n_pages + kOpTile - 1) / kOpTile);
   if (blockIdx.x >= n_tiles) return;
-  const uint32_t my_tiles = (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x;  // tiles k = 0 .. my_tiles-1
   load_tables(tabs);  // all warps fill the tables; ends with __syncthreads
   if (warp == 0) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(
@@ -698,47 +738,42 @@ k_pack_onepass(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ ima
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
-  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  tmem_fence_before();
   __syncthreads();
-  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  tmem_fence_after();
   const uint32_t tmem_base = sh.tmem_base;
 
   if (warp < kOpWarps) {
-    // ---------------------------------------------------------------- compute warps
+    // ---------------------------------------------------------------- compute warps (two warpgroups, most registers)
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kOpComputeRegs));
     const uint32_t g = lane >> 3, l = lane & 7, lane4 = lane * 4;
     // this warp's TMEM window: its quadrant's 32 lanes, 256 columns (two halves of 128) at (warp / 4) * 256
     const uint32_t tm = tmem_base + (((warp & 3) * 32) << 16) + (warp >> 2) * 256;
-    auto drain = [&](uint32_t half) {  // the warp's four pages of that half: TMEM -> their slots
-      const int s = sh.slot[half][warp * 4 + g];
-      uint4* d = packed + (uint64_t)(s < 0 ? 0 : s) * 256 + l;
-      const bool any = __any_sync(0xFFFFFFFFu, s >= 0);
-      if (any) {
-#pragma unroll 1
-        for (int jb = 0; jb < 32; jb += 8) {  // eight steps per round trip to TMEM, then their eight stores
-          uint4 v[8];
-#pragma unroll
-          for (int j = 0; j < 8; j++) v[j] = tmem_ld4(tm + half * 128 + 4 * (jb + j));
-          tmem_wait_ld();
-          if (s >= 0) {
-#pragma unroll
-            for (int j = 0; j < 8; j++) stg_stream(d + 8 * (jb + j), v[j]);
-          }
-        }
-      }
-    };
-    uint4 ring[kRing];
-    uint64_t p = ((uint64_t)blockIdx.x * kOpTile) + warp * 4 + g;
+    // Tiles k * grid + blockIdx: no CTA's parked tile ever waits for a tile that has not been started (tickets taken
+    // ahead of time did: measured 23 ms against 11)
+    uint32_t id = blockIdx.x, id_next = blockIdx.x + gridDim.x;
+    uint4 ring[kOpRing];
+    uint64_t p = (uint64_t)id * kOpTile + warp * 4 + g;
     const uint4* src = image + p * 256 + l;
     ring_fill(ring, src, p < n_pages);
-    for (uint32_t k = 0; k < my_tiles; k++) {
+    uint32_t k = 0;
+    for (;; k++) {
       const uint32_t half = k & 1;
+      if (id >= n_tiles) break;
+      OP_T(t0);
+      if (k >= 2) {  // the half still holds tile k - 2 until the drain warps are done with it
+        bar_sync(kBarDrained + half, kCntDrained);
+        tmem_fence_after();
+      }
+      OP_TD(t1, sh.slot[half][0]);
+      if (threadIdx.x == 0) sh.tile_of_half[half] = id;
       PageAcc a;
       a.z = 0;
       a.h = 0;
       const bool on = p < n_pages;
-      const uint64_t p_next = p + (uint64_t)gridDim.x * kOpTile;
+      const uint64_t p_next = (uint64_t)id_next * kOpTile + warp * 4 + g;
       const uint4* src_next = image + p_next * 256 + l;
-      const bool next_on = k + 1 < my_tiles && p_next < n_pages;
+      const bool next_on = id_next < n_tiles && p_next < n_pages;
       const uint32_t tcol = tm + half * 128;
       page_pass<true, true>(a, ring, src, on, src_next, next_on, lane4, [&](auto jc, const uint4& v) {
         constexpr int j = decltype(jc)::value;
@@ -758,42 +793,101 @@ k_pack_onepass(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ ima
         if (on) {
           crc[p] = page_crc;
           hash[p] = page_hash;
+          if (z) {  // the control warp will claim this page's table slot: have the lines in L2 by then
+            const uint64_t home = table_home(page_hash, t.mask);
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(t.keys + home));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(t.vals + home));
+          }
         }
       }
       tmem_wait_st();
-      __threadfence_block();
-      bar_arrive(kBarComputed + half, kOpWarps * 32 + 32);  // the control warp of this parity takes it from here
-      if (k >= 1) {  // the previous tile's verdict has had a whole tile's time to arrive
-        bar_sync(kBarDecided + (half ^ 1), kOpWarps * 32 + 32);
-        drain(half ^ 1);
-      }
+      tmem_fence_before();
+      bar_sync(kBarCompute, kOpWarps * 32);  // thread 0's tile_of_half before anyone's arrival
+      bar_arrive(kBarComputed + half, kCntComputed);  // the control warp of this parity takes it from here
+      OP_T(t2);
+      OP_ADD(0, t1, t2);
+      OP_ADD(1, t0, t1);
+      id = id_next;
+      id_next += gridDim.x;
       p = p_next;
       src = src_next;
     }
-    const uint32_t last = (my_tiles - 1) & 1;
-    bar_sync(kBarDecided + last, kOpWarps * 32 + 32);
-    drain(last);
-  } else {
+    // out of tiles: tell both control warps (and through them the drain warps), meeting the drain warps' last arrivals
+    for (uint32_t e = 0; e < 2; e++, k++) {
+      const uint32_t half = k & 1;
+      if (k >= 2) bar_sync(kBarDrained + half, kCntDrained);
+      if (threadIdx.x == 0) sh.tile_of_half[half] = kOpNoTile;
+      bar_sync(kBarCompute, kOpWarps * 32);
+      bar_arrive(kBarComputed + half, kCntComputed);
+    }
+  } else if (warp >= 12) {
+    // ---------------------------------------------------------------- drain warps: TMEM quadrant warp % 4
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kOpOtherRegs));
+    const uint32_t g = lane >> 3, l = lane & 7, q = warp & 3;
+    for (uint32_t k = 0;; k++) {
+      const uint32_t half = k & 1;
+      OP_T(d0);
+      bar_sync(kBarDecided + half, kCntDecided);
+      tmem_fence_after();
+      if (sh.tile_of_half[half] == kOpNoTile) {  // out of tiles; the other half's notice is the next thing to come
+        bar_sync(kBarDecided + (half ^ 1), kCntDecided);
+        break;
+      }
+      OP_TD(d1, sh.slot[half][q * 4 + g]);
+#pragma unroll 1
+      for (uint32_t cw = q; cw < (uint32_t)kOpWarps; cw += 4) {  // the compute warps that share this quadrant
+        const uint32_t tm = tmem_base + ((q * 32) << 16) + (cw >> 2) * 256 + half * 128;
+        const int s = sh.slot[half][cw * 4 + g];
+        uint4* d = packed + (uint64_t)(s < 0 ? 0 : s) * 256 + l;
+        if (!__any_sync(0xFFFFFFFFu, s >= 0)) continue;
+#pragma unroll 1
+        for (int jb = 0; jb < 32; jb += 8) {  // eight steps per round trip to TMEM, then their eight stores
+          uint4 v[8];
+#pragma unroll
+          for (int j = 0; j < 8; j++) v[j] = tmem_ld4(tm + 4 * (jb + j));
+          tmem_wait_ld();
+          if (s >= 0) {
+#pragma unroll
+            for (int j = 0; j < 8; j++) stg_stream(d + 8 * (jb + j), v[j]);
+          }
+        }
+      }
+      tmem_fence_before();
+      bar_arrive(kBarDrained + half, kCntDrained);
+      OP_T(d2);
+      if (warp == 12 && lane == 0) {
+        OP_ADD_RAW(2, d1, d2);
+        OP_ADD_RAW(3, d0, d1);
+      }
+    }
+  } else if (warp < kOpWarps + 2) {
     // ---------------------------------------------------------------- control warps: lane i <-> page i of the tile
-    const uint32_t half = warp - kOpWarps;  // control warp 0: even tiles (TMEM half 0), control warp 1: odd tiles
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kOpOtherRegs));
+    const uint32_t half = warp - kOpWarps;  // control warp 0: the tiles parked in TMEM half 0, control warp 1: half 1
     const uint32_t lt_mask = (1u << lane) - 1;
     uint32_t n_kind[5] = {0, 0, 0, 0, 0};
     uint32_t wm = 0;  // every tile below wm is known to have inserted
-    for (uint32_t k = half; k < my_tiles; k += 2) {
-      const uint32_t tile = k * gridDim.x + blockIdx.x;
+    for (;;) {
+      OP_T(c0);
+      bar_sync(kBarComputed + half, kCntComputed);
+      const uint32_t tile = sh.tile_of_half[half];
+      if (tile == kOpNoTile) {
+        bar_arrive(kBarDecided + half, kCntDecided);
+        break;
+      }
       const uint64_t p = (uint64_t)tile * kOpTile + lane;
-      bar_sync(kBarComputed + half, kOpWarps * 32 + 32);
       const uint32_t nz = sh.nonzero[half][lane];
+      OP_TD(c1, nz);
       const unsigned long long h = sh.hash[half][lane];
       const uint32_t my_crc = sh.crc[half][lane];
       uint64_t sl = 0;
       if (nz == 1u) {
         const uint32_t v = kOriginSelf << 26 | (uint32_t)p;
         for (sl = table_home(h, t.mask);; sl = (sl + 1) & t.mask) {
-          unsigned long long key = t.keys[sl];
-          if (key == 0ull) key = atomicCAS(&t.keys[sl], 0ull, h);
+          // one round trip: the CAS claims an empty slot or tells whose it is (most slots are met empty)
+          const unsigned long long key = atomicCAS(&t.keys[sl], 0ull, h);
           if (key == 0ull || key == h) {
-            if (key == 0ull || __ldcg(&t.vals[sl]) > v) atomicMin(&t.vals[sl], v);
+            if (key == 0ull || __ldcg(&t.vals[sl]) > v) atomicMin(&t.vals[sl], v);  // no result used: a RED
             break;
           }
         }
@@ -801,6 +895,7 @@ k_pack_onepass(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ ima
       __threadfence();  // the tile's crc / hash stores (seen through the barrier) and table atomics before the flag
       __syncwarp();
       if (lane == 0) st_status(&status[tile], kStInserted);
+      OP_T(c2);
       // every earlier tile must have inserted before an owner can be read
       for (uint32_t b0 = wm; b0 < tile; b0 += 128) {
         for (;;) {
@@ -817,6 +912,7 @@ k_pack_onepass(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ ima
       }
       wm = tile;
       __threadfence();
+      OP_T(c3);
       // verdict
       uint32_t out = 0u;  // zero page
       bool keep = false;
@@ -837,25 +933,54 @@ k_pack_onepass(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ ima
       const uint32_t bal = __ballot_sync(0xFFFFFFFFu, keep);
       const uint32_t total = __popc(bal), rank = __popc(bal & lt_mask);
       if (lane == 0) st_status(&status[tile], (tile == 0 ? kStPrefix : kStAgg) | total);
+      OP_T(c4);
       uint32_t excl = 0;
       if (tile > 0) {
+        // decoupled look-back, 128 tiles per round trip (in step with each other, a whole round of CTAs publishes
+        // its counts at about the same time: the nearest prefix is usually a round away)
         int64_t look = (int64_t)tile - 1;
         for (;;) {
-          const int64_t idx = look - lane;
-          unsigned long long st;
+          unsigned long long st[4];
           for (;;) {
-            st = idx >= 0 ? ld_status(&status[idx]) : kStPrefix;
-            if (!__any_sync(0xFFFFFFFFu, (st >> 62) < 2)) break;
+            bool ready = true;
+#pragma unroll
+            for (int b = 0; b < 4; b++) {
+              const int64_t idx = look - 32 * b - lane;
+              st[b] = idx >= 0 ? ld_status(&status[idx]) : kStPrefix;
+              ready = ready && (st[b] >> 62) >= 2;
+            }
+            // a batch beyond the nearest prefix need not be ready: only what lies in front of it counts
+            uint32_t need = 0xFFFFFFFFu;
+            bool done = false, ok = true;
+#pragma unroll
+            for (int b = 0; b < 4; b++) {
+              const uint32_t pre = __ballot_sync(0xFFFFFFFFu, (st[b] >> 62) == 3);
+              const uint32_t unr = __ballot_sync(0xFFFFFFFFu, (st[b] >> 62) < 2);
+              if (!done) {
+                const uint32_t upto = pre ? ((2u << (__ffs(pre) - 1)) - 1u) : 0xFFFFFFFFu;  // lanes up to the first prefix
+                if (unr & upto) ok = false;
+                if (pre) done = true;
+              }
+            }
+            (void)need;
+            (void)ready;
+            if (ok) break;
             __nanosleep(40);
           }
-          const uint32_t incl = __ballot_sync(0xFFFFFFFFu, (st >> 62) == 3);
-          const uint32_t upto = incl ? (uint32_t)__ffs(incl) - 1u : 31u;
-          uint32_t v = lane <= upto ? (uint32_t)st : 0u;
+          bool found = false;
 #pragma unroll
-          for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
-          excl += v;
-          if (incl) break;
-          look -= 32;
+          for (int b = 0; b < 4; b++) {
+            if (found) break;
+            const uint32_t incl = __ballot_sync(0xFFFFFFFFu, (st[b] >> 62) == 3);
+            const uint32_t upto = incl ? (uint32_t)__ffs(incl) - 1u : 31u;
+            uint32_t v = lane <= upto ? (uint32_t)st[b] : 0u;
+#pragma unroll
+            for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
+            excl += v;
+            found = incl != 0;
+          }
+          if (found) break;
+          look -= 128;
         }
         if (lane == 0) st_status(&status[tile], kStPrefix | (excl + total));
       }
@@ -876,7 +1001,13 @@ k_pack_onepass(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ ima
       }
       sh.slot[half][lane] = sv;
       __threadfence_block();
-      bar_arrive(kBarDecided + half, kOpWarps * 32 + 32);
+      bar_arrive(kBarDecided + half, kCntDecided);
+      OP_T(c5);
+      OP_ADD(8, c0, c1);
+      OP_ADD(9, c1, c2);
+      OP_ADD(10, c2, c3);
+      OP_ADD(11, c3, c4);
+      OP_ADD(12, c4, c5);
     }
 #pragma unroll
     for (int q = 0; q < 5; q++) {
@@ -885,8 +1016,10 @@ k_pack_onepass(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ ima
       for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
       if (lane == 0 && v) atomicAdd(&cnt->kind[q], (unsigned long long)v);
     }
+  } else {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kOpOtherRegs));  // warps 10, 11: only fill the warpgroup
   }
-  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  tmem_fence_before();
   __syncthreads();
   if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
 }
@@ -1037,6 +1170,16 @@ cudaError_t configure_kernels() {
 }
 
 uint32_t onepass_tile_pages() { return kOpTile; }
+
+#ifdef GRIT_OP_PROF
+extern "C" void grit_op_prof(unsigned long long* out, int reset) {  // development aid, not in the ABI
+  cudaMemcpyFromSymbol(out, g_op_prof, sizeof(g_op_prof));
+  if (reset) {
+    unsigned long long z[16] = {};
+    cudaMemcpyToSymbol(g_op_prof, z, sizeof z);
+  }
+}
+#endif
 
 cudaError_t launch_pack_onepass(const LaunchGeom& g, const Gf2Tables* d_tab, const void* d_image, uint64_t n_pages,
                                 uint32_t* d_crc, uint64_t* d_hash, uint32_t* d_ref, DedupTable t, PeerCrcs crcs, void* d_packed,
