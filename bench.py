@@ -721,6 +721,11 @@ def run_gritpack(args):
                "api": "grit_pack_host + grit_restore_host (pinned host buffers, 64 MiB chunks, 3 streams)"
                       + ("; each rank packs its own image, no cross-rank references on this path" if world > 1 else "")}
         del h_img, h_packed, h_out
+        hr = None
+        try:                                   # give the pinned blocks back to the OS: the legs below want the memory
+            torch._C._host_emptyCache()
+        except Exception:
+            pass
 
     # ---- e2e_dir: the reference's own boundary (TransferData on directories), N = 1
     e2e_dir = None
@@ -787,15 +792,28 @@ def restore_stress(torch, dist, ctx, rank, world, link_h2d):
     free, _ = torch.cuda.mem_get_info()
     avail = psutil.virtual_memory().available
     piece = (2 * GiB) // PAGE
-    n_pages = min(int(180e9) // PAGE, (free - 8 * GiB) // PAGE, int(avail * 0.55 / max(world, 1) / 0.78) // PAGE, (1 << 26) - 1)
-    n_pages = n_pages // piece * piece
-    if n_pages < piece:
-        return {"skipped": f"free HBM {free >> 30} GiB, host memory {avail >> 30} GiB"}
+    # the packed stream sits in pinned host memory: more than half of a box's memory cannot be pinned by one process,
+    # and eight processes pinning at once get less each
+    share = 0.55 if world == 1 else 0.3
+    n_pages = min(int(180e9) // PAGE, (free - 8 * GiB) // PAGE, int(avail * share / max(world, 1) / 0.78) // PAGE, (1 << 26) - 1)
+    n_pages = max(n_pages // piece * piece, 0)
+    h_packed = None
+    while n_pages >= piece and h_packed is None:
+        try:
+            h_packed = torch.empty(int(n_pages * 0.79) * PAGE, dtype=torch.uint8, pin_memory=True)
+        except Exception:                       # the OS refused to pin that much: try half
+            n_pages = n_pages // 2 // piece * piece
+    if h_packed is None:                        # still take part in what the other ranks wait for
+        n_pages = 0
+        if world > 1:
+            dist.barrier()
+            dist.all_reduce(torch.zeros(1, device=dev), op=dist.ReduceOp.MAX)
+            dist.all_reduce(torch.zeros(1, dtype=torch.int64, device=dev))
+        return {"skipped": f"free HBM {free >> 30} GiB, host memory {avail >> 30} GiB: no pinned memory to be had"}
     out = torch.empty(n_pages * PAGE, dtype=torch.uint8, device=dev)
     tmp = torch.empty(piece * PAGE, dtype=torch.uint8, device=dev)
     h_ref = torch.empty(n_pages, dtype=torch.int32)
     h_crc = torch.empty(n_pages, dtype=torch.int32)
-    h_packed = torch.empty(int(n_pages * 0.79) * PAGE, dtype=torch.uint8, pin_memory=True)
     seed, lib = 0x5EED5 + rank, ctx.lib
     slots, mix = 0, {"n_zero": 0, "n_dup": 0}
 
@@ -835,9 +853,12 @@ def restore_stress(torch, dist, ctx, rank, world, link_h2d):
         synth(again, p0, piece)
         assert torch.equal(out[p0 * PAGE:(p0 + piece) * PAGE], again), f"restore stress: pages {p0}.. differ"
     n_bytes, u_bytes = n_pages * PAGE, slots * PAGE
-    return {"image_bytes_per_gpu": n_bytes, "pages": n_pages, "packed_bytes": u_bytes,
+    sizes = torch.tensor([n_bytes], dtype=torch.int64, device=dev)
+    if world > 1:
+        dist.all_reduce(sizes)                     # ranks may have ended up with different sizes
+    return {"image_bytes_per_gpu": n_bytes, "image_bytes_all_ranks": int(sizes.item()), "pages": n_pages, "packed_bytes": u_bytes,
             "page_mix": {"n_zero": mix["n_zero"], "n_dup": mix["n_dup"], "n_data": slots},
-            "seconds": round(dt, 3), "image_gbs_all_ranks": round(world * n_bytes / dt / 1e9, 2),
+            "seconds": round(dt, 3), "image_gbs_all_ranks": round(int(sizes.item()) / dt / 1e9, 2),
             "h2d_gbs_per_gpu": round(u_bytes / dt / 1e9, 2),
             "frac_of_h2d_link": round(u_bytes / dt / 1e9 / link_h2d, 3) if link_h2d else None,
             "kernel_ms": round(st["gpu_ms"], 1), "n_bad": st["n_bad"], "bit_exact": True,

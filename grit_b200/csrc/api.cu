@@ -193,6 +193,7 @@ int analyze_through_async(grit_ctx* ctx, const void* d_image, uint64_t n_pages, 
                           uint32_t* d_ref, void* d_packed, uint64_t capacity_pages, cudaStream_t s, char* err,
                           size_t errlen) {
   GRIT_CUDA(cudaMemsetAsync(&ctx->d_cnt->first_drop, 0xFF, sizeof(unsigned long long), s));
+  GRIT_CUDA(cudaMemsetAsync(&ctx->d_cnt->through_from, 0, sizeof(unsigned long long), s));
   GRIT_CUDA(launch_probe_dense(d_image, n_pages, ctx->d_cnt, s));  // sets dense_hint
   GRIT_CUDA(launch_analyze_auto(ctx->geom, ctx->d_tables, d_image, n_pages, d_crc, d_hash, d_ref, d_packed, capacity_pages, 0,
                                 ctx->d_cnt, s));

@@ -222,18 +222,37 @@ int grit_pack_buffer_ranked(grit_comm* c, const void* d_image, uint64_t n_pages,
   }
   LaunchGeom k1_geom = ctx->geom;  // leave NCCL its SMs while slices are still in flight
   if (W > 1) k1_geom.sm_count = std::max(1, ctx->geom.sm_count - comm_ctas());
-  // Rank 0 refers to no other rank: without a parent its image may be dense (weights, optimizer state) and K1 can
-  // store the pages to their own slots as in grit_pack_buffer.  The ranks above mostly hold pages rank 0 owns.
-  const bool try_through = c->rank == 0 && !(parent && parent->n_pages) && n_pages && d_packed && write_through_pack();
+  // Without a parent the image may be dense (weights, optimizer state) and K1 can store the pages to their own slots
+  // as in grit_pack_buffer.  Rank 0 refers to no other rank: its own sample decides.  A rank above 0 may hold what a
+  // lower rank holds (replicated weights: nearly all PEER references, nothing to write through) or not (sharded
+  // state): it analyses its first slice plainly, and once that slice's tables have been exchanged a look at the
+  // lower ranks' hashes at the same page indices settles it for the slices that follow.
+  const bool try_through = !(parent && parent->n_pages) && n_pages && d_packed && write_through_pack() &&
+                           (c->rank == 0 || n_slices >= 4);
+  const uint64_t through_from = try_through && c->rank > 0 ? L : 0;
   if (try_through) {
     GRIT_CUDA(cudaMemsetAsync(&ctx->d_cnt->first_drop, 0xFF, sizeof(unsigned long long), s));
+    GRIT_CUDA(cudaMemcpyAsync(&ctx->d_cnt->through_from, &through_from, sizeof(uint64_t), cudaMemcpyHostToDevice, s));
     GRIT_CUDA(launch_probe_dense(d_image, n_pages, ctx->d_cnt, s));
     ctx->launches++;
   }
 
   for (uint64_t i = 0; i < std::max<uint64_t>(n_slices, 1); i++) {
     const uint64_t p0 = i << shift, have = p0 < n_pages ? std::min(L, n_pages - p0) : 0;
-    if (have && try_through) {
+    if (have && try_through && p0 >= through_from) {
+      if (i == 1 && c->rank > 0) {  // the first slice of every lower rank has arrived: do they hold what this rank holds?
+        cudaEvent_t first_done = c->ev_slice[n_slices - 1];  // a spare event: the last slice records it again later
+        GRIT_CUDA(cudaEventRecord(first_done, cs));
+        GRIT_CUDA(cudaStreamWaitEvent(s, first_done, 0));
+        ProbeLists first{};
+        for (int r = 0; r < c->rank; r++) {
+          first.hash[1 + r].base = reinterpret_cast<const unsigned long long*>(hash_all) + (uint64_t)r * L;
+          first.n[1 + r] = L;
+        }
+        GRIT_CUDA(launch_peer_overlap_hint(reinterpret_cast<const unsigned long long*>(d_hash), first, std::min(L, n_pages),
+                                           ctx->d_cnt, s));
+        ctx->launches++;
+      }
       GRIT_CUDA(launch_analyze_auto(k1_geom, ctx->d_tables, static_cast<const char*>(d_image) + p0 * kPage, have, d_crc + p0,
                                     d_hash + p0, d_ref + p0, static_cast<char*>(d_packed) + p0 * kPage, capacity_pages, p0,
                                     ctx->d_cnt, s));

@@ -599,7 +599,7 @@ k_compact(const uint4* __restrict__ image, uint64_t n_pages, uint32_t* __restric
     // after a write-through K1 a tile whose pages all keep their own index is already in place
     const uint64_t tile_base = (uint64_t)tile * kCompactTile;
     const uint32_t tile_pages = (uint32_t)(n_pages - tile_base < kCompactTile ? n_pages - tile_base : kCompactTile);
-    const bool tile_in_place = in_place && first_slot == tile_base && total == tile_pages;
+    const bool tile_in_place = in_place && first_slot == tile_base && total == tile_pages && tile_base >= cnt->through_from;
     // copy: one page per warp per step, two steps in flight
     for (uint32_t k = tile_in_place ? total : warp; k < total; k += 16) {
       const uint32_t k2 = k + 8;
@@ -1207,6 +1207,31 @@ cudaError_t launch_analyze(const LaunchGeom& g, const Gf2Tables* d_tab, const vo
 cudaError_t launch_probe_dense(const void* d_image, uint64_t n_pages, DevCounters* d_cnt, cudaStream_t s) {
   if (!n_pages) return cudaSuccess;
   k_probe_dense<<<1, 1024, 0, s>>>(static_cast<const uint4*>(d_image), n_pages, d_cnt);
+  return cudaGetLastError();
+}
+
+__global__ void __launch_bounds__(1024)
+k_peer_overlap_hint(const unsigned long long* __restrict__ hash, ProbeLists lists, uint64_t n, DevCounters* __restrict__ cnt) {
+  __shared__ uint32_t s_match;
+  if (threadIdx.x == 0) s_match = 0;
+  __syncthreads();
+  const uint64_t samples = n < 8192 ? n : 8192;
+  for (uint64_t i = threadIdx.x; i < samples; i += blockDim.x) {
+    const uint64_t p = i * n / samples;
+    const unsigned long long h = hash[p];
+    bool m = false;
+    for (int o = 1; o < 9; o++)
+      if (lists.hash[o] && p < lists.n[o] && lists.hash[o][p] == h) m = true;
+    if (m) atomicAdd(&s_match, 1u);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0 && s_match * 16 > samples) cnt->dense_hint = 0u;
+}
+
+cudaError_t launch_peer_overlap_hint(const unsigned long long* d_hash, const ProbeLists& lists, uint64_t n, DevCounters* d_cnt,
+                                     cudaStream_t s) {
+  if (!n) return cudaSuccess;
+  k_peer_overlap_hint<<<1, 1024, 0, s>>>(d_hash, lists, n, d_cnt);
   return cudaGetLastError();
 }
 

@@ -82,6 +82,7 @@ struct DevCounters {
   unsigned long long first_drop;      // lowest zero page K1 has seen (UINT64_MAX: none); storing stops above it
   unsigned int dense_hint;            // 1: the sampled pages held no zero page and K1 wrote the pages through
   unsigned int pad2;
+  unsigned long long through_from;    // first page K1 wrote through (pages in front of it were only analysed)
 };
 
 struct LaunchGeom {
@@ -101,6 +102,12 @@ cudaError_t launch_compact(const LaunchGeom& g, const void* d_image, uint64_t n_
                            void* d_packed, uint64_t capacity_pages, uint64_t slot_base, bool chained,
                            unsigned long long* d_tile_status, DevCounters* d_cnt, cudaStream_t s,
                            bool in_place = false);
+// Ranks above 0 of a ranked pack: after the first slice's tables have been exchanged, compare this rank's hashes with
+// the lower ranks' at the same page index.  Replicated state (weights) sits at the same offsets on every rank: many
+// matches mean the image will mostly turn into PEER references and writing it through would be wasted
+// (dense_hint := 0); none mean the ranks hold different data (sharded state) and the local sample's verdict stands.
+cudaError_t launch_peer_overlap_hint(const unsigned long long* d_hash, const ProbeLists& lists, uint64_t n, DevCounters* d_cnt,
+                                     cudaStream_t s);
 // sample of the image -> d_cnt->dense_hint: is writing the pages through to their own slots worth it
 cudaError_t launch_probe_dense(const void* d_image, uint64_t n_pages, DevCounters* d_cnt, cudaStream_t s);
 // K1 for a full image: write-through variant when the hint says dense, plain K1 otherwise.  d_image, the per-page
