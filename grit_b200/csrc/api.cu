@@ -15,17 +15,13 @@ int ensure_table(grit_ctx* ctx, uint64_t n_items, DedupTable* t, char* err, size
   uint64_t cap = 1024;
   while (cap < 2 * n_items) cap <<= 1;
   if (cap > ctx->table_cap) {
-    if (ctx->d_keys) cudaFree(ctx->d_keys);
-    if (ctx->d_vals) cudaFree(ctx->d_vals);
-    ctx->d_keys = nullptr;
-    ctx->d_vals = nullptr;
+    if (ctx->d_slots) cudaFree(ctx->d_slots);
+    ctx->d_slots = nullptr;
     ctx->table_cap = 0;
-    GRIT_CUDA(cudaMalloc(&ctx->d_keys, cap * sizeof(unsigned long long)));
-    GRIT_CUDA(cudaMalloc(&ctx->d_vals, cap * sizeof(uint32_t)));
+    GRIT_CUDA(cudaMalloc(&ctx->d_slots, cap * sizeof(TableSlot)));
     ctx->table_cap = cap;
   }
-  t->keys = ctx->d_keys;
-  t->vals = ctx->d_vals;
+  t->slots = ctx->d_slots;
   t->mask = cap - 1;
   return GRIT_OK;
 }
@@ -109,8 +105,8 @@ int dedup_views_async(grit_ctx* ctx, uint64_t n_pages, const uint32_t* d_crc, co
                       cudaEvent_t lists_ready) {
   DedupTable t{};
   if (int rc = ensure_table(ctx, n_pages, &t, err, errlen)) return rc;
-  GRIT_CUDA(cudaMemsetAsync(t.keys, 0, (t.mask + 1) * sizeof(unsigned long long), s));
-  GRIT_CUDA(cudaMemsetAsync(t.vals, 0xFF, (t.mask + 1) * sizeof(uint32_t), s));
+  GRIT_CUDA(launch_table_clear(ctx->geom, t, s));
+  ctx->launches++;
   GRIT_CUDA(launch_table_insert(ctx->geom, t, d_hash, d_ref, n_pages, kOriginSelf, 0, s));
   ctx->launches++;
   bool any = false;
@@ -120,7 +116,7 @@ int dedup_views_async(grit_ctx* ctx, uint64_t n_pages, const uint32_t* d_crc, co
     GRIT_CUDA(launch_table_probe_lists(ctx->geom, t, lists, s));
     ctx->launches++;
   }
-  GRIT_CUDA(launch_resolve(ctx->geom, t, 0, n_pages, d_crc, d_hash, d_ref, crcs, s));
+  GRIT_CUDA(launch_resolve(ctx->geom, t, 0, n_pages, d_crc, d_hash, d_ref, crcs, ctx->d_cnt, s));
   ctx->launches++;
   return GRIT_OK;
 }
@@ -172,8 +168,8 @@ int dedup_async(grit_ctx* ctx, uint64_t n_pages, const uint32_t* d_crc, const ui
   for (uint32_t r = 0; r < n_peers; r++) items += peers[r].n_pages;
   DedupTable t{};
   if (int rc = ensure_table(ctx, items, &t, err, errlen)) return rc;
-  GRIT_CUDA(cudaMemsetAsync(t.keys, 0, (t.mask + 1) * sizeof(unsigned long long), s));
-  GRIT_CUDA(cudaMemsetAsync(t.vals, 0xFF, (t.mask + 1) * sizeof(uint32_t), s));
+  GRIT_CUDA(launch_table_clear(ctx->geom, t, s));
+  ctx->launches++;
   if (parent_on) {
     GRIT_CUDA(launch_table_insert(ctx->geom, t, parent->hash, nullptr, parent->n_pages, 0, 0, s));
     ctx->launches++;
@@ -191,10 +187,11 @@ int dedup_async(grit_ctx* ctx, uint64_t n_pages, const uint32_t* d_crc, const ui
 // K1 with the dense sample and write-through into d_packed; remembers the buffers for the K3 that follows
 int analyze_through_async(grit_ctx* ctx, const void* d_image, uint64_t n_pages, uint32_t* d_crc, uint64_t* d_hash,
                           uint32_t* d_ref, void* d_packed, uint64_t capacity_pages, cudaStream_t s, char* err,
-                          size_t errlen) {
+                          size_t errlen, bool probed = false) {
   GRIT_CUDA(cudaMemsetAsync(&ctx->d_cnt->first_drop, 0xFF, sizeof(unsigned long long), s));
   GRIT_CUDA(cudaMemsetAsync(&ctx->d_cnt->through_from, 0, sizeof(unsigned long long), s));
-  GRIT_CUDA(launch_probe_dense(d_image, n_pages, ctx->d_cnt, s));  // sets dense_hint
+  GRIT_CUDA(cudaMemsetAsync(&ctx->d_cnt->n_nonkeep, 0, sizeof(unsigned int), s));
+  if (!probed) GRIT_CUDA(launch_probe_dense(d_image, n_pages, ctx->d_cnt, s));  // sets dense_hint
   GRIT_CUDA(launch_analyze_auto(ctx->geom, ctx->d_tables, d_image, n_pages, d_crc, d_hash, d_ref, d_packed, capacity_pages, 0,
                                 ctx->d_cnt, s));
   ctx->launches += 3;  // probe + the two K1 variants, one of which returns at once
@@ -288,8 +285,7 @@ void grit_ctx_destroy(grit_ctx* ctx) {
     if (b.p) cudaFree(b.p);
   for (auto& b : ctx->pin)
     if (b.p) cudaFreeHost(b.p);
-  if (ctx->d_keys) cudaFree(ctx->d_keys);
-  if (ctx->d_vals) cudaFree(ctx->d_vals);
+  if (ctx->d_slots) cudaFree(ctx->d_slots);
   if (ctx->d_status) cudaFree(ctx->d_status);
   if (ctx->d_tables) cudaFree(ctx->d_tables);
   if (ctx->d_cnt) cudaFree(ctx->d_cnt);
@@ -411,7 +407,8 @@ int grit_pack_buffer(grit_ctx* ctx, const void* d_image, uint64_t n_pages, const
     ctx->launches++;
   } else {
     if (path == kThrough) {
-      if (int rc = analyze_through_async(ctx, d_image, n_pages, d_crc, d_hash, d_ref, d_packed, capacity_pages, s, err, errlen))
+      if (int rc = analyze_through_async(ctx, d_image, n_pages, d_crc, d_hash, d_ref, d_packed, capacity_pages, s, err, errlen,
+                                         true))
         return rc;
     } else {
       GRIT_CUDA(launch_analyze(ctx->geom, ctx->d_tables, d_image, n_pages, d_crc, d_hash, d_ref, s));

@@ -233,6 +233,7 @@ int grit_pack_buffer_ranked(grit_comm* c, const void* d_image, uint64_t n_pages,
   if (try_through) {
     GRIT_CUDA(cudaMemsetAsync(&ctx->d_cnt->first_drop, 0xFF, sizeof(unsigned long long), s));
     GRIT_CUDA(cudaMemcpyAsync(&ctx->d_cnt->through_from, &through_from, sizeof(uint64_t), cudaMemcpyHostToDevice, s));
+    GRIT_CUDA(cudaMemsetAsync(&ctx->d_cnt->n_nonkeep, 0, sizeof(unsigned int), s));
     GRIT_CUDA(launch_probe_dense(d_image, n_pages, ctx->d_cnt, s));
     ctx->launches++;
   }

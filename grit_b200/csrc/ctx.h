@@ -21,8 +21,7 @@ struct grit_ctx {
   grit::DevCounters* d_cnt = nullptr;
   grit::DevCounters* h_cnt = nullptr;  // pinned mirror
   // scratch, grown on demand and kept for the life of the context
-  unsigned long long* d_keys = nullptr;
-  uint32_t* d_vals = nullptr;
+  grit::TableSlot* d_slots = nullptr;
   uint64_t table_cap = 0;
   unsigned long long* d_status = nullptr;
   uint64_t status_cap = 0;

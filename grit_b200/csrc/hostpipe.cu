@@ -95,8 +95,8 @@ int PackStream::begin(const grit_table* parent, char* err, size_t errlen, const 
   if (int rc = ensure_status(ctx_, chunk_pages_, err, errlen)) return rc;
   cudaStream_t s = ctx_->stream;
   if (int rc = reset_counters(ctx_, s, err, errlen)) return rc;
-  GRIT_CUDA(cudaMemsetAsync(table_.keys, 0, (table_.mask + 1) * sizeof(unsigned long long), s));
-  GRIT_CUDA(cudaMemsetAsync(table_.vals, 0xFF, (table_.mask + 1) * sizeof(uint32_t), s));
+  GRIT_CUDA(launch_table_clear(ctx_->geom, table_, s));
+  ctx_->launches++;
   if (parent && parent->n_pages) {
     GRIT_CUDA(launch_table_insert(ctx_->geom, table_, d_parent_hash_, nullptr, parent->n_pages, 0, 0, s));
     ctx_->launches++;
@@ -155,7 +155,7 @@ int PackStream::submit(uint64_t i, const void* h_src, uint64_t n_pages, char* er
   GRIT_CUDA(cudaMemsetAsync(&ctx_->d_cnt->ticket, 0, 3 * sizeof(unsigned int), s));  // ticket and its neighbours
   GRIT_CUDA(launch_analyze(ctx_->geom, ctx_->d_tables, d_in_[b], n_pages, d_crc_ + p0, d_hash_ + p0, d_ref_ + p0, s));
   GRIT_CUDA(launch_table_insert(ctx_->geom, table_, d_hash_ + p0, d_ref_ + p0, n_pages, kOriginSelf, p0, s));
-  GRIT_CUDA(launch_resolve(ctx_->geom, table_, p0, p0 + n_pages, d_crc_, d_hash_, d_ref_, crcs_, s));
+  GRIT_CUDA(launch_resolve(ctx_->geom, table_, p0, p0 + n_pages, d_crc_, d_hash_, d_ref_, crcs_, ctx_->d_cnt, s));
   GRIT_CUDA(launch_compact(ctx_->geom, d_in_[b], n_pages, d_ref_ + p0, d_out_[b], chunk_pages_, 0, true,
                            ctx_->d_status, ctx_->d_cnt, s));
   ctx_->launches += 4;

@@ -384,21 +384,32 @@ k_probe_dense(const uint4* __restrict__ image, uint64_t n_pages, DevCounters* __
     s_repeats = 0;
   }
   __syncthreads();
-  for (uint32_t i = threadIdx.x; i < kProbeSamples; i += blockDim.x) {
-    const uint64_t p = (uint64_t)i * n_pages / kProbeSamples;
-    if (i && p == (uint64_t)(i - 1) * n_pages / kProbeSamples) continue;  // fewer pages than samples
-    const uint4* q = image + p * 256 + (i & 31);  // eight 16-byte pieces, 512 bytes apart; the offset varies by sample
+  // four samples per thread, their 32 loads issued before any is used (one block: latency is all this kernel costs)
+  constexpr int kPer = kProbeSamples / 1024;
+  uint4 v[kPer][8];
+  uint64_t pg[kPer];
+#pragma unroll
+  for (int q = 0; q < kPer; q++) {
+    const uint32_t i = threadIdx.x + 1024 * q;
+    pg[q] = (uint64_t)i * n_pages / kProbeSamples;
+    const uint4* src = image + pg[q] * 256 + (i & 31);  // eight 16-byte pieces, 512 bytes apart; the offset varies by sample
+#pragma unroll
+    for (int k = 0; k < 8; k++) v[q][k] = __ldg(src + 32 * k);
+  }
+#pragma unroll
+  for (int q = 0; q < kPer; q++) {
+    const uint32_t i = threadIdx.x + 1024 * q;
+    if (i && pg[q] == (uint64_t)(i - 1) * n_pages / kProbeSamples) continue;  // fewer pages than samples
     uint32_t o = 0;
     unsigned long long sig = kGold;
 #pragma unroll
     for (int k = 0; k < 8; k++) {
-      const uint4 v = __ldg(q + 32 * k);
-      o |= v.x | v.y | v.z | v.w;
-      sig = (sig ^ ((unsigned long long)v.y << 32 | v.x)) * kFmul;
-      sig = (sig ^ ((unsigned long long)v.w << 32 | v.z)) * kFmul;
+      o |= v[q][k].x | v[q][k].y | v[q][k].z | v[q][k].w;
+      sig = (sig ^ ((unsigned long long)v[q][k].y << 32 | v[q][k].x)) * kFmul;
+      sig = (sig ^ ((unsigned long long)v[q][k].w << 32 | v[q][k].z)) * kFmul;
     }
     if (o == 0) {  // reads as a zero page
-      atomicMin(&s_first_zero, (unsigned long long)p);
+      atomicMin(&s_first_zero, (unsigned long long)pg[q]);
       continue;
     }
     // the sampled bytes differ with the offset, so two samples only compare equal when they read the same offset of
@@ -427,6 +438,13 @@ __device__ __forceinline__ uint64_t table_home(unsigned long long h, uint64_t ma
 }
 
 __global__ void __launch_bounds__(256)
+k_table_clear(DedupTable t) {
+  uint4* w = reinterpret_cast<uint4*>(t.slots);
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i <= t.mask; i += (uint64_t)gridDim.x * blockDim.x)
+    stg_stream(w + i, make_uint4(0u, 0u, 0xFFFFFFFFu, 0u));
+}
+
+__global__ void __launch_bounds__(256)
 k_table_insert(DedupTable t, const unsigned long long* __restrict__ hash, const uint32_t* __restrict__ ref,
                uint64_t n, uint32_t origin, uint64_t index_base) {
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
@@ -435,12 +453,12 @@ k_table_insert(DedupTable t, const unsigned long long* __restrict__ hash, const 
     const unsigned long long h = hash[i];
     const uint32_t v = origin << 26 | (uint32_t)(index_base + i);
     for (uint64_t s = table_home(h, t.mask);; s = (s + 1) & t.mask) {
-      unsigned long long k = t.keys[s];
-      if (k == 0ull) k = atomicCAS(&t.keys[s], 0ull, h);
+      unsigned long long k = t.slots[s].key;
+      if (k == 0ull) k = atomicCAS(&t.slots[s].key, 0ull, h);
       if (k == 0ull || k == h) {
         // a much-repeated page (a pool of identical buffers) sends hundreds of pages to one slot: only a value
         // that lowers the owner is worth an atomic, and the plain read costs a hit in L2
-        if (k == 0ull || __ldcg(&t.vals[s]) > v) atomicMin(&t.vals[s], v);
+        if (k == 0ull || __ldcg(&t.slots[s].val) > v) atomicMin(&t.slots[s].val, v);
         break;
       }
     }
@@ -460,10 +478,10 @@ k_table_probe_lists(DedupTable t, ProbeLists lists) {
     const unsigned long long h = hash[i];
     if (h == 0ull) continue;  // hash64 is never 0: padding of a gathered slice, or a damaged hashes.bin
     for (uint64_t s = table_home(h, t.mask);; s = (s + 1) & t.mask) {
-      const unsigned long long k = t.keys[s];
+      const unsigned long long k = t.slots[s].key;
       if (k == h) {
         const uint32_t v = origin << 26 | (uint32_t)i;
-        if (__ldcg(&t.vals[s]) > v) atomicMin(&t.vals[s], v);
+        if (__ldcg(&t.slots[s].val) > v) atomicMin(&t.slots[s].val, v);
         break;
       }
       if (k == 0ull) break;
@@ -473,14 +491,14 @@ k_table_probe_lists(DedupTable t, ProbeLists lists) {
 
 __global__ void __launch_bounds__(256)
 k_resolve(DedupTable t, uint64_t page0, uint64_t page1, const uint32_t* __restrict__ crc,
-          const unsigned long long* __restrict__ hash, uint32_t* __restrict__ ref, PeerCrcs crcs) {
+          const unsigned long long* __restrict__ hash, uint32_t* __restrict__ ref, PeerCrcs crcs, DevCounters* __restrict__ cnt) {
   for (uint64_t p = page0 + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; p < page1;
        p += (uint64_t)gridDim.x * blockDim.x) {
     if (ref[p] == 0u) continue;
     const unsigned long long h = hash[p];
     uint64_t s = table_home(h, t.mask);
-    while (t.keys[s] != h) s = (s + 1) & t.mask;  // inserted by k_table_insert
-    const uint32_t v = t.vals[s], origin = v >> 26, idx = v & ((1u << 26) - 1);
+    while (t.slots[s].key != h) s = (s + 1) & t.mask;  // inserted by k_table_insert
+    const uint32_t v = t.slots[s].val, origin = v >> 26, idx = v & ((1u << 26) - 1);
     uint32_t out = kRefKeep;
     if (!(origin == kOriginSelf && idx == (uint32_t)p)) {
       const uint32_t ocrc = origin == 0             ? crcs.parent[idx]
@@ -493,6 +511,7 @@ k_resolve(DedupTable t, uint64_t page0, uint64_t page1, const uint32_t* __restri
       }
     }
     ref[p] = out;
+    if (out != kRefKeep) atomicAdd(&cnt->n_nonkeep, 1u);  // rare in the images where K3 asks (dense ones)
   }
 }
 
@@ -517,6 +536,19 @@ k_compact(const uint4* __restrict__ image, uint64_t n_pages, uint32_t* __restric
           unsigned long long* __restrict__ status, DevCounters* __restrict__ cnt) {
   __shared__ uint32_t s_tile, s_warp_cnt[8], s_excl;
   in_place = in_place && cnt->dense_hint;  // the write-through K1 ran: pages in front of the first drop are in place
+  // Nothing was dropped at all (no zero page met, no reference made): every page is stored, in its own slot, where the
+  // write-through K1 already put it.  No scan, no look-back: one streaming pass over ref.
+  if (in_place && cnt->through_from == 0 && cnt->first_drop == ~0ull && cnt->n_nonkeep == 0u) {
+    for (uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n_pages; p += (uint64_t)gridDim.x * blockDim.x)
+      ref[p] = 1u << 29 | (uint32_t)p;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+      cnt->kind[1] = n_pages;
+      cnt->n_stored = n_pages;
+      cnt->slot_base_next = n_pages;
+      if (n_pages > capacity_pages) cnt->overflow = n_pages - capacity_pages;
+    }
+    return;
+  }
   __shared__ uint16_t s_list[kCompactTile];
   const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const uint32_t n_tiles = (uint32_t)((n_pages + kCompactTile - 1) / kCompactTile);
@@ -795,8 +827,7 @@ k_pack_onepass(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ ima
           hash[p] = page_hash;
           if (z) {  // the control warp will claim this page's table slot: have the lines in L2 by then
             const uint64_t home = table_home(page_hash, t.mask);
-            asm volatile("prefetch.global.L2 [%0];" ::"l"(t.keys + home));
-            asm volatile("prefetch.global.L2 [%0];" ::"l"(t.vals + home));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(t.slots + home));
           }
         }
       }
@@ -885,9 +916,9 @@ k_pack_onepass(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ ima
         const uint32_t v = kOriginSelf << 26 | (uint32_t)p;
         for (sl = table_home(h, t.mask);; sl = (sl + 1) & t.mask) {
           // one round trip: the CAS claims an empty slot or tells whose it is (most slots are met empty)
-          const unsigned long long key = atomicCAS(&t.keys[sl], 0ull, h);
+          const unsigned long long key = atomicCAS(&t.slots[sl].key, 0ull, h);
           if (key == 0ull || key == h) {
-            if (key == 0ull || __ldcg(&t.vals[sl]) > v) atomicMin(&t.vals[sl], v);  // no result used: a RED
+            if (key == 0ull || __ldcg(&t.slots[sl].val) > v) atomicMin(&t.slots[sl].val, v);  // no result used: a RED
             break;
           }
         }
@@ -917,7 +948,7 @@ k_pack_onepass(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ ima
       uint32_t out = 0u;  // zero page
       bool keep = false;
       if (nz == 1u) {
-        const uint32_t v = __ldcg(&t.vals[sl]), origin = v >> 26, idx = v & ((1u << 26) - 1);
+        const uint32_t v = __ldcg(&t.slots[sl].val), origin = v >> 26, idx = v & ((1u << 26) - 1);
         out = kRefKeep;
         if (!(origin == kOriginSelf && idx == (uint32_t)p)) {
           const uint32_t ocrc = origin == 0             ? crcs.parent[idx]
@@ -1248,6 +1279,11 @@ cudaError_t launch_analyze_auto(const LaunchGeom& g, const Gf2Tables* d_tab, con
   return cudaGetLastError();
 }
 
+cudaError_t launch_table_clear(const LaunchGeom& g, DedupTable t, cudaStream_t s) {
+  k_table_clear<<<grid_for(g, t.mask + 1, 256, 8), 256, 0, s>>>(t);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_table_insert(const LaunchGeom& g, DedupTable t, const uint64_t* d_hash,
                                 const uint32_t* d_ref_or_null, uint64_t n, uint32_t origin, uint64_t index_base,
                                 cudaStream_t s) {
@@ -1268,10 +1304,10 @@ cudaError_t launch_table_probe_lists(const LaunchGeom& g, DedupTable t, const Pr
 }
 
 cudaError_t launch_resolve(const LaunchGeom& g, DedupTable t, uint64_t page0, uint64_t page1, const uint32_t* d_crc,
-                           const uint64_t* d_hash, uint32_t* d_ref, PeerCrcs crcs, cudaStream_t s) {
+                           const uint64_t* d_hash, uint32_t* d_ref, PeerCrcs crcs, DevCounters* d_cnt, cudaStream_t s) {
   if (page1 <= page0) return cudaSuccess;
   k_resolve<<<grid_for(g, page1 - page0, 256, 8), 256, 0, s>>>(
-      t, page0, page1, d_crc, reinterpret_cast<const unsigned long long*>(d_hash), d_ref, crcs);
+      t, page0, page1, d_crc, reinterpret_cast<const unsigned long long*>(d_hash), d_ref, crcs, d_cnt);
   return cudaGetLastError();
 }
 

@@ -16,9 +16,14 @@ constexpr uint32_t kOriginSelf = 15;
 constexpr uint32_t kCompactTile = 256;  // pages per compaction tile
 
 // table[hash64] = lowest (origin << 26 | page index); origin 0 parent, 1+r peer r, 15 self
+// key and owner share a 16-byte slot: one DRAM sector per insert, probe or look-up instead of two
+struct TableSlot {
+  unsigned long long key;  // 0 = empty
+  uint32_t val;            // lowest (origin << 26 | page index) seen for the key
+  uint32_t pad;
+};
 struct DedupTable {
-  unsigned long long* keys;  // 0 = empty
-  uint32_t* vals;
+  TableSlot* slots;
   uint64_t mask;  // capacity - 1, capacity a power of two
 };
 
@@ -81,7 +86,7 @@ struct DevCounters {
   // so that a later K3 on the same buffers can see how K1 went
   unsigned long long first_drop;      // lowest zero page K1 has seen (UINT64_MAX: none); storing stops above it
   unsigned int dense_hint;            // 1: the sampled pages held no zero page and K1 wrote the pages through
-  unsigned int pad2;
+  unsigned int n_nonkeep;             // K2 since that K1: pages that became DUP / PARENT / PEER references
   unsigned long long through_from;    // first page K1 wrote through (pages in front of it were only analysed)
 };
 
@@ -92,12 +97,13 @@ struct LaunchGeom {
 cudaError_t launch_analyze(const LaunchGeom& g, const Gf2Tables* d_tab, const void* d_image,
                            uint64_t n_pages, uint32_t* d_crc, uint64_t* d_hash, uint32_t* d_ref,
                            cudaStream_t s);
+cudaError_t launch_table_clear(const LaunchGeom& g, DedupTable t, cudaStream_t s);  // every key 0, every owner 0xFFFFFFFF
 cudaError_t launch_table_insert(const LaunchGeom& g, DedupTable t, const uint64_t* d_hash,
                                 const uint32_t* d_ref_or_null, uint64_t n, uint32_t origin,
                                 uint64_t index_base, cudaStream_t s);
 cudaError_t launch_table_probe_lists(const LaunchGeom& g, DedupTable t, const ProbeLists& lists, cudaStream_t s);
 cudaError_t launch_resolve(const LaunchGeom& g, DedupTable t, uint64_t page0, uint64_t page1, const uint32_t* d_crc,
-                           const uint64_t* d_hash, uint32_t* d_ref, PeerCrcs crcs, cudaStream_t s);
+                           const uint64_t* d_hash, uint32_t* d_ref, PeerCrcs crcs, DevCounters* d_cnt, cudaStream_t s);
 cudaError_t launch_compact(const LaunchGeom& g, const void* d_image, uint64_t n_pages, uint32_t* d_ref,
                            void* d_packed, uint64_t capacity_pages, uint64_t slot_base, bool chained,
                            unsigned long long* d_tile_status, DevCounters* d_cnt, cudaStream_t s,
