@@ -386,14 +386,17 @@ int grit_pack_buffer(grit_ctx* ctx, const void* d_image, uint64_t n_pages, const
   bool staged = false;
   ctx->through_image = nullptr;
   if (n_pages && d_packed) {
-    if (full && write_through_pack()) {  // the sample decides on the device; the host needs the answer to pick kernels
-      GRIT_CUDA(launch_probe_dense(d_image, n_pages, ctx->d_cnt, s));
-      ctx->launches++;
-      GRIT_CUDA(cudaMemcpyAsync(&ctx->h_cnt->dense_hint, &ctx->d_cnt->dense_hint, sizeof(unsigned int), cudaMemcpyDeviceToHost, s));
-      GRIT_CUDA(cudaStreamSynchronize(s));
-      if (ctx->h_cnt->dense_hint) path = kThrough;
+    if (full && write_through_pack()) path = kThrough;  // the sample decides on the device which K1 variant runs
+    if (onepass_pack()) {  // a different kernel sequence: the host needs the sample's answer, at the price of a sync
+      path = kOnepass;
+      if (full && write_through_pack()) {
+        GRIT_CUDA(launch_probe_dense(d_image, n_pages, ctx->d_cnt, s));
+        ctx->launches++;
+        GRIT_CUDA(cudaMemcpyAsync(&ctx->h_cnt->dense_hint, &ctx->d_cnt->dense_hint, sizeof(unsigned int), cudaMemcpyDeviceToHost, s));
+        GRIT_CUDA(cudaStreamSynchronize(s));
+        if (ctx->h_cnt->dense_hint) path = kThrough;
+      }
     }
-    if (path != kThrough && onepass_pack()) path = kOnepass;
   }
   if (path == kOnepass) {
     DedupTable t{};
@@ -408,7 +411,7 @@ int grit_pack_buffer(grit_ctx* ctx, const void* d_image, uint64_t n_pages, const
   } else {
     if (path == kThrough) {
       if (int rc = analyze_through_async(ctx, d_image, n_pages, d_crc, d_hash, d_ref, d_packed, capacity_pages, s, err, errlen,
-                                         true))
+                                         onepass_pack()))
         return rc;
     } else {
       GRIT_CUDA(launch_analyze(ctx->geom, ctx->d_tables, d_image, n_pages, d_crc, d_hash, d_ref, s));
@@ -442,7 +445,7 @@ int grit_pack_buffer(grit_ctx* ctx, const void* d_image, uint64_t n_pages, const
       cudaEventElapsedTime(&ms, ctx->evB, ctx->ev1);
       stats->stage_ms[2] = ms;
     }
-    stats->wrote_through = path == kThrough ? 1 : (path == kOnepass ? 2 : 0);
+    stats->wrote_through = path == kThrough ? (c.dense_hint ? 1 : 0) : (path == kOnepass ? 2 : 0);
   }
   if (c.overflow)
     return fail(err, errlen, GRIT_EINVAL, "packed buffer too small: %llu pages did not fit capacity %llu",
