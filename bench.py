@@ -442,6 +442,9 @@ def run_gritpack(args):
         mine = need_mask.clone()
         dist.all_reduce(need_mask, op=dist.ReduceOp.MAX)
         imgs = [None] * rank
+        torch.cuda.synchronize()
+        dist.barrier()
+        t_stage = time.perf_counter()
         for q in range(world):
             if not int(need_mask[q]):
                 continue
@@ -453,8 +456,13 @@ def run_gritpack(args):
             else:
                 comm.broadcast(restored, root=q)
         torch.cuda.synchronize()
+        dist.barrier()
+        stage_info["seconds"] = round(time.perf_counter() - t_stage, 4)
+        stage_info["images"] = int(need_mask.sum().item())
+        stage_info["bytes_per_rank"] = stage_info["images"] * n_bytes
         return imgs
 
+    stage_info = {}
     r = pack_step()
     if world > 1:
         peer_images = stage_peer_images(r["ref"])
@@ -763,6 +771,9 @@ def run_gritpack(args):
                            "beside K1; PEER pages restored from the owner's image staged in local HBM before the "
                            "timed region (grit_comm_broadcast)") if world > 1 else "none (1 GPU)",
             "selftest": ({"passed": True} | selftest) if selftest else None,
+            "peer_image_staging": (stage_info | {"how": "grit_comm_broadcast (NCCL) of every image some rank's PEER references "
+                                                        "name, once, before the timed region; not part of `value`"})
+            if world > 1 else None,
             "pack_gbs": round(world * n_bytes / (t_pack * 1e-3) / 1e9, 1),
             "restore_gbs": round(world * n_bytes / (t_restore * 1e-3) / 1e9, 1),
             "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "e2e_dir": e2e_dir, "other_mixes": other,
