@@ -88,6 +88,24 @@ int comm_ctas() {  // SMs left to NCCL while K1 runs (= the CTAs the communicato
   return v;
 }
 
+int comm_reserve() {  // SMs K1 leaves free while the exchange runs (default: as many as NCCL has CTAs)
+  static const int v = [] {
+    const char* e = getenv("GRITPACK_COMM_RESERVE");
+    const int n = e ? atoi(e) : -1;
+    return n >= 0 && n <= 64 ? n : comm_ctas();
+  }();
+  return v;
+}
+
+int comm_slices() {  // about this many slices per image
+  static const int v = [] {
+    const char* e = getenv("GRITPACK_COMM_SLICES");
+    const int n = e ? atoi(e) : 0;
+    return n >= 1 && n <= 64 ? n : 8;
+  }();
+  return v;
+}
+
 }  // namespace
 
 struct grit_comm {
@@ -201,7 +219,7 @@ int grit_pack_buffer_ranked(grit_comm* c, const void* d_image, uint64_t n_pages,
   }
   // slices of 2^shift pages: about eight per image, at least 4096 pages each
   uint32_t shift = 12;
-  while (shift < 26 && (max_pages >> shift) > 8) shift++;
+  while (shift < 26 && (max_pages >> shift) > (uint64_t)comm_slices()) shift++;
   const uint64_t L = 1ull << shift, n_slices = (max_pages + L - 1) >> shift;
   uint64_t *hash_all = nullptr, *pad_hash = nullptr;
   uint32_t *crc_all = nullptr, *pad_crc = nullptr;
@@ -221,7 +239,7 @@ int grit_pack_buffer_ranked(grit_comm* c, const void* d_image, uint64_t n_pages,
     }
   }
   LaunchGeom k1_geom = ctx->geom;  // leave NCCL its SMs while slices are still in flight
-  if (W > 1) k1_geom.sm_count = std::max(1, ctx->geom.sm_count - comm_ctas());
+  if (W > 1) k1_geom.sm_count = std::max(1, ctx->geom.sm_count - comm_reserve());
   // Without a parent the image may be dense (weights, optimizer state) and K1 can store the pages to their own slots
   // as in grit_pack_buffer.  Rank 0 refers to no other rank: its own sample decides.  A rank above 0 may hold what a
   // lower rank holds (replicated weights: nearly all PEER references, nothing to write through) or not (sharded

@@ -5,6 +5,7 @@ Prints, per 32-page tile and averaged over the CTAs, how long the compute warps 
 drain, and how long a control warp waits for the tile, inserts, waits for earlier tiles, reads owners and looks back."""
 import ctypes as C
 import sys, os
+os.environ.setdefault("GRITPACK_ONEPASS", "1")
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from grit_b200 import _lib
