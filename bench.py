@@ -728,6 +728,33 @@ def run_gritpack(args):
                         "restore the stored pages up and the image down",
                "api": "grit_pack_host + grit_restore_host (pinned host buffers, 64 MiB chunks, 3 streams)"
                       + ("; each rank packs its own image, no cross-rank references on this path" if world > 1 else "")}
+        # the link carries what is stored, not what is there: the same calls on the other two page mixes (N = 1)
+        if world == 1 and not args.no_extra:
+            def e2e_of(img_dev, parent_host=None, parent_tab=None, reps=2):
+                h_img.copy_(img_dev[:hb])
+                q = ctx.pack_host(h_img, parent=parent_tab, packed=h_packed)
+                ctx.restore_host(q["packed"], q["ref"], q["crc"], parent_image=parent_host, out=h_out)
+                assert torch.equal(h_out, h_img), "e2e (other mix) restored image differs"
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                for _ in range(reps):
+                    q = ctx.pack_host(h_img, parent=parent_tab, packed=h_packed)
+                    t1 = time.perf_counter()
+                    ctx.restore_host(q["packed"], q["ref"], q["crc"], parent_image=parent_host, out=h_out)
+                torch.cuda.synchronize()
+                dt = (time.perf_counter() - t0) / reps
+                return {"value": round(2 * hb / dt / 1e9, 2), "unit": "GB/s", "stored_bytes": int(q["stats"]["n_data"]) * PAGE,
+                        "seconds_per_step": round(dt, 3)}
+            mix_img = ctx.synth_image(e2e_pages, seed=0xC0FFEE)
+            e2e["c1_mix_10zero_15dup"] = e2e_of(mix_img)
+            del mix_img
+            base_tab = ctx.pack_host(h_img.copy_(image[:hb]), packed=h_packed)
+            parent_host = torch.empty(hb, dtype=torch.uint8, pin_memory=True).copy_(image[:hb])
+            child = dirty_copy(torch, image[:hb], e2e_pages, rank)
+            e2e["incremental_5pct_dirty"] = e2e_of(child, parent_host=parent_host, parent_tab=(base_tab["hash"], base_tab["crc"]))
+            e2e["incremental_5pct_dirty"]["note"] = ("the pack uploads the image and downloads 5 % of it; the restore uploads the "
+                                                     "parent image (host memory) as well and downloads the whole image")
+            del child, parent_host, base_tab
         del h_img, h_packed, h_out
         hr = None
         try:                                   # give the pinned blocks back to the OS: the legs below want the memory

@@ -223,9 +223,16 @@ __device__ __forceinline__ unsigned long long finish_hash(const PageAcc& a, uint
   return v ? v : 1ull;
 }
 
+#ifndef GRIT_K1_WARPS
+#define GRIT_K1_WARPS 16
+#endif
+#ifndef GRIT_K1_RING
+#define GRIT_K1_RING 16
+#endif
+constexpr int kK1Warps = GRIT_K1_WARPS, kK1Threads = kK1Warps * 32, kK1Ring = GRIT_K1_RING;
 // ------------------------------------------------------------------ K1 analyze
 // A warp takes four consecutive pages per step; lanes 8g..8g+7 own page g.
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kK1Threads, 1)
 k_analyze(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ image, uint64_t n_pages,
           uint32_t* __restrict__ crc, unsigned long long* __restrict__ hash, uint32_t* __restrict__ ref,
           const DevCounters* __restrict__ cnt, int want_hint) {
@@ -234,11 +241,11 @@ k_analyze(const Gf2Tables* __restrict__ tabs, const uint4* __restrict__ image, u
   const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const uint32_t g = lane >> 3, l = lane & 7, lane4 = lane * 4;
   const uint64_t n_groups = (n_pages + 3) / 4;
-  const uint64_t stride = (uint64_t)gridDim.x * kWarps;
-  uint64_t grp = (uint64_t)blockIdx.x * kWarps + warp;
+  const uint64_t stride = (uint64_t)gridDim.x * kK1Warps;
+  uint64_t grp = (uint64_t)blockIdx.x * kK1Warps + warp;
   if (grp >= n_groups) return;
 
-  uint4 ring[kRing];
+  uint4 ring[kK1Ring];
   uint64_t p = 4 * grp + g;
   const uint4* src = image + p * 256 + l;
   ring_fill(ring, src, p < n_pages);
@@ -1226,9 +1233,9 @@ cudaError_t launch_pack_onepass(const LaunchGeom& g, const Gf2Tables* d_tab, con
 cudaError_t launch_analyze(const LaunchGeom& g, const Gf2Tables* d_tab, const void* d_image, uint64_t n_pages,
                            uint32_t* d_crc, uint64_t* d_hash, uint32_t* d_ref, cudaStream_t s) {
   if (!n_pages) return cudaSuccess;
-  const int grid = grid_for(g, (n_pages + 3) / 4, kWarps, 1);
-  k_analyze<<<grid, kThreads, kSmBytes, s>>>(d_tab, static_cast<const uint4*>(d_image), n_pages, d_crc,
-                                             reinterpret_cast<unsigned long long*>(d_hash), d_ref, nullptr, -1);
+  const int grid = grid_for(g, (n_pages + 3) / 4, kK1Warps, 1);
+  k_analyze<<<grid, kK1Threads, kSmBytes, s>>>(d_tab, static_cast<const uint4*>(d_image), n_pages, d_crc,
+                                               reinterpret_cast<unsigned long long*>(d_hash), d_ref, nullptr, -1);
   return cudaGetLastError();
 }
 
@@ -1274,8 +1281,8 @@ cudaError_t launch_analyze_auto(const LaunchGeom& g, const Gf2Tables* d_tab, con
   k_analyze_through<<<grid, kThreads, kSmBytesWT, s>>>(d_tab, static_cast<const uint4*>(d_image), n_pages, d_crc,
                                                        reinterpret_cast<unsigned long long*>(d_hash), d_ref,
                                                        static_cast<uint4*>(d_packed), capacity_pages, page_base, d_cnt, 1);
-  k_analyze<<<grid, kThreads, kSmBytes, s>>>(d_tab, static_cast<const uint4*>(d_image), n_pages, d_crc,
-                                             reinterpret_cast<unsigned long long*>(d_hash), d_ref, d_cnt, 0);
+  k_analyze<<<grid_for(g, (n_pages + 3) / 4, kK1Warps, 1), kK1Threads, kSmBytes, s>>>(
+      d_tab, static_cast<const uint4*>(d_image), n_pages, d_crc, reinterpret_cast<unsigned long long*>(d_hash), d_ref, d_cnt, 0);
   return cudaGetLastError();
 }
 
