@@ -9,7 +9,7 @@
 //   kernel stream   K1(slice 0) K1(slice 1) ... K1(last)  insert own hashes | probe with lower ranks' lists  resolve  K3
 //   comm stream          all-gather(slice 0) all-gather(slice 1) ...   all-gather(last) ^
 // K1 runs in slices of 2^shift pages; as soon as a slice's hashes exist its all-gather starts on the comm stream, so
-// all but the last slice's exchange hides behind K1.  K1 leaves a few SMs free for NCCL's CTAs while a communicator
+// all but the last slice's exchange hides behind K1.  K1 leaves 16 SMs free for NCCL's 16 CTAs while a communicator
 // is in use (its grid is one persistent CTA per SM and would otherwise keep NCCL's kernels waiting for a free SM).
 // Gathered slices stay where NCCL put them ([slice][rank][2^shift]); K2 reads them through ListView.
 //
@@ -83,7 +83,7 @@ int comm_ctas() {  // SMs left to NCCL while K1 runs (= the CTAs the communicato
   static const int v = [] {
     const char* e = getenv("GRITPACK_COMM_CTAS");
     const int n = e ? atoi(e) : 0;
-    return n >= 1 && n <= 32 ? n : 8;
+    return n >= 1 && n <= 32 ? n : 16;
   }();
   return v;
 }
@@ -97,11 +97,13 @@ int comm_reserve() {  // SMs K1 leaves free while the exchange runs (default: as
   return v;
 }
 
+// Measured on 8 x B200, configs[2] image, ms per pack on the slowest rank: 8 CTAs / 8 SMs / 8 slices 4.98;
+// 16 / 16 / 8: 4.69; 32 CTAs on 8 reserved SMs: 5.15; 8 / 8 / 16: 5.14; 16 / 16 / 16: 4.55
 int comm_slices() {  // about this many slices per image
   static const int v = [] {
     const char* e = getenv("GRITPACK_COMM_SLICES");
     const int n = e ? atoi(e) : 0;
-    return n >= 1 && n <= 64 ? n : 8;
+    return n >= 1 && n <= 64 ? n : 16;
   }();
   return v;
 }
