@@ -79,34 +79,18 @@ int load_nccl(char* err, size_t errlen) {
       return fail(err, errlen, GRIT_ECUDA, "%s: %s (%s:%d)", #call, g_nccl.GetErrorString(r_), __FILE__, __LINE__); \
   } while (0)
 
-int comm_ctas() {  // SMs left to NCCL while K1 runs (= the CTAs the communicator may use)
-  static const int v = [] {
-    const char* e = getenv("GRITPACK_COMM_CTAS");
-    const int n = e ? atoi(e) : 0;
-    return n >= 1 && n <= 32 ? n : 16;
-  }();
-  return v;
+// How much of the GPU the exchange gets.  Measured, slowest rank's pack of the configs[2] image: on 8 x B200 8 NCCL CTAs
+// on 8 SMs K1 leaves free with 8 slices 4.98 ms, 16 / 16 / 8 4.69, 32 CTAs on 8 SMs 5.15 (NCCL's CTAs wait for SMs),
+// 8 / 8 / 16 5.14, 16 / 16 / 16 4.55; on 2 x B200 8 / 8 / 8 4.42 ms, 16 / 16 / 16 4.68 (the tables are a quarter of the
+// size and the SMs are missed by rank 0's write-through K1).  So: 8 up to two ranks, 16 beyond.
+int env_int(const char* name, int lo, int hi, int dflt) {
+  const char* e = getenv(name);
+  const int n = e ? atoi(e) : lo - 1;
+  return n >= lo && n <= hi ? n : dflt;
 }
-
-int comm_reserve() {  // SMs K1 leaves free while the exchange runs (default: as many as NCCL has CTAs)
-  static const int v = [] {
-    const char* e = getenv("GRITPACK_COMM_RESERVE");
-    const int n = e ? atoi(e) : -1;
-    return n >= 0 && n <= 64 ? n : comm_ctas();
-  }();
-  return v;
-}
-
-// Measured on 8 x B200, configs[2] image, ms per pack on the slowest rank: 8 CTAs / 8 SMs / 8 slices 4.98;
-// 16 / 16 / 8: 4.69; 32 CTAs on 8 reserved SMs: 5.15; 8 / 8 / 16: 5.14; 16 / 16 / 16: 4.55
-int comm_slices() {  // about this many slices per image
-  static const int v = [] {
-    const char* e = getenv("GRITPACK_COMM_SLICES");
-    const int n = e ? atoi(e) : 0;
-    return n >= 1 && n <= 64 ? n : 16;
-  }();
-  return v;
-}
+int comm_ctas(int world) { return env_int("GRITPACK_COMM_CTAS", 1, 32, world <= 2 ? 8 : 16); }  // NCCL's CTAs
+int comm_reserve(int world) { return env_int("GRITPACK_COMM_RESERVE", 0, 64, comm_ctas(world)); }  // SMs K1 leaves free
+int comm_slices(int world) { return env_int("GRITPACK_COMM_SLICES", 1, 64, world <= 2 ? 8 : 16); }  // slices per image
 
 }  // namespace
 
@@ -172,7 +156,7 @@ int grit_comm_create(grit_ctx* ctx, int rank, int world, const void* id, grit_co
   ncclUniqueId u;
   memcpy(&u, id, sizeof u);
   ncclConfig_t cfg = NCCL_CONFIG_INITIALIZER;
-  cfg.maxCTAs = comm_ctas();  // the table exchange is small; K1 leaves exactly this many SMs free for it
+  cfg.maxCTAs = comm_ctas(world);  // the table exchange is small; K1 leaves exactly this many SMs free for it
   const ncclResult_t r = g_nccl.CommInitRankConfig(&c->nccl, world, u, rank, &cfg);
   if (r != ncclSuccess) return bail(fail(err, errlen, GRIT_ECUDA, "ncclCommInitRankConfig: %s", g_nccl.GetErrorString(r)));
   *out = c;
@@ -221,7 +205,7 @@ int grit_pack_buffer_ranked(grit_comm* c, const void* d_image, uint64_t n_pages,
   }
   // slices of 2^shift pages: about eight per image, at least 4096 pages each
   uint32_t shift = 12;
-  while (shift < 26 && (max_pages >> shift) > (uint64_t)comm_slices()) shift++;
+  while (shift < 26 && (max_pages >> shift) > (uint64_t)comm_slices(W)) shift++;
   const uint64_t L = 1ull << shift, n_slices = (max_pages + L - 1) >> shift;
   uint64_t *hash_all = nullptr, *pad_hash = nullptr;
   uint32_t *crc_all = nullptr, *pad_crc = nullptr;
@@ -241,7 +225,7 @@ int grit_pack_buffer_ranked(grit_comm* c, const void* d_image, uint64_t n_pages,
     }
   }
   LaunchGeom k1_geom = ctx->geom;  // leave NCCL its SMs while slices are still in flight
-  if (W > 1) k1_geom.sm_count = std::max(1, ctx->geom.sm_count - comm_reserve());
+  if (W > 1) k1_geom.sm_count = std::max(1, ctx->geom.sm_count - comm_reserve(W));
   // Without a parent the image may be dense (weights, optimizer state) and K1 can store the pages to their own slots
   // as in grit_pack_buffer.  Rank 0 refers to no other rank: its own sample decides.  A rank above 0 may hold what a
   // lower rank holds (replicated weights: nearly all PEER references, nothing to write through) or not (sharded
