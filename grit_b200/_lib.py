@@ -76,9 +76,12 @@ SYMBOLS = {
     "grit_ctx_destroy": (None, [_P]),
     "grit_ctx_launches": (_U64, [_P]),
     "grit_warmup": (_I, [_I]),
+    "grit_ctx_set_option": (_I, [_P, C.c_char_p, _U64]),
+    "grit_ctx_dup_mismatches": (_U64, [_P]),
     "grit_analyze_pages": (_I, [_P, _P, _U64, _P, _P, _P, _P] + _ERR),
     "grit_analyze_pages_through": (_I, [_P, _P, _U64, _P, _P, _P, _P, _U64, _P] + _ERR),
     "grit_dedup_pages": (_I, [_P, _U64, _P, _P, _P, C.POINTER(Table), C.POINTER(Table), _U32, _P] + _ERR),
+    "grit_verify_dup_pages": (_I, [_P, _P, _U64, _P, C.POINTER(_U64), _P] + _ERR),
     "grit_compact_pages": (_I, [_P, _P, _U64, _P, _P, _U64, _U64, C.POINTER(_U64), _P] + _ERR),
     "grit_compact_pages_static": (_I, [_I, _P, _U64, _P, _P, _U64, _U64, C.POINTER(_U64), _P] + _ERR),
     "grit_compact_pages_static_warmup": (_I, [_I] + _ERR),

@@ -37,6 +37,15 @@ class Context:
 
     __del__ = close
 
+    def set_option(self, name, value):
+        """grit_ctx_set_option, e.g. ("verify_dup_bytes", 1)."""
+        if self.lib.grit_ctx_set_option(self.handle, name.encode(), int(value)) != 0:
+            raise GritError(_lib.EINVAL, f"unknown context option {name!r}")
+
+    @property
+    def dup_mismatches(self):
+        return int(self.lib.grit_ctx_dup_mismatches(self.handle))
+
     @property
     def launches(self):
         return int(self.lib.grit_ctx_launches(self.handle))
@@ -98,6 +107,13 @@ class Context:
                                              C.byref(ptab) if ptab else None, arr, len(peers), _stream(), err,
                                              len(err)), err)
         return ref
+
+    def verify_dups(self, image, ref):
+        """grit_verify_dup_pages: DUP references whose bytes differ from their owner's go back to "store"; -> how many."""
+        n, err = C.c_uint64(0), _lib.errbuf()
+        _lib.check(self.lib.grit_verify_dup_pages(self.handle, _ptr(image), self._pages(image), _ptr(ref), C.byref(n), _stream(),
+                                                  err, len(err)), err)
+        return int(n.value)
 
     # -- K3
     def compact(self, image, ref, packed, slot_base=0):

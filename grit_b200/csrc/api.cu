@@ -262,6 +262,7 @@ int grit_ctx_create(int device, grit_ctx** out, char* err, size_t errlen) {
   CTX_CUDA(cudaEventCreate(&ctx->evB));
   CTX_CUDA(cudaMalloc(&ctx->d_tables, sizeof(Gf2Tables)));
   CTX_CUDA(cudaMalloc(&ctx->d_cnt, sizeof(DevCounters)));
+  CTX_CUDA(cudaMemset(ctx->d_cnt, 0, sizeof(DevCounters)));
   CTX_CUDA(cudaMallocHost(&ctx->h_cnt, sizeof(DevCounters)));
   {
     Gf2Tables* h = new (std::nothrow) Gf2Tables();
@@ -309,6 +310,23 @@ int grit_warmup(int device) {
 
 uint64_t grit_ctx_launches(const grit_ctx* ctx) { return ctx ? ctx->launches : 0; }
 
+int grit_ctx_set_option(grit_ctx* ctx, const char* name, uint64_t value) {
+  if (!ctx || !name) return GRIT_EINVAL;
+  if (!strcmp(name, "verify_dup_bytes")) {
+    ctx->verify_dup_bytes = value != 0;
+    return GRIT_OK;
+  }
+  return GRIT_EINVAL;
+}
+
+uint64_t grit_ctx_dup_mismatches(grit_ctx* ctx) {
+  if (!ctx) return 0;
+  unsigned long long v = 0;
+  cudaSetDevice(ctx->device);
+  cudaMemcpy(&v, &ctx->d_cnt->dup_mismatch, sizeof v, cudaMemcpyDeviceToHost);
+  return v;
+}
+
 int grit_analyze_pages(grit_ctx* ctx, const void* d_image, uint64_t n_pages, uint32_t* d_crc, uint64_t* d_hash,
                        uint32_t* d_ref, void* stream, char* err, size_t errlen) {
   if (int rc = enter(ctx, err, errlen)) return rc;
@@ -342,6 +360,23 @@ int grit_dedup_pages(grit_ctx* ctx, uint64_t n_pages, const uint32_t* d_crc, con
   if (n_pages && (!d_crc || !d_hash || !d_ref)) return fail(err, errlen, GRIT_EINVAL, "null buffer");
   std::lock_guard<std::mutex> g(ctx->mu);
   return dedup_async(ctx, n_pages, d_crc, d_hash, d_ref, parent, peers, n_peers, pick(ctx, stream), err, errlen);
+}
+
+int grit_verify_dup_pages(grit_ctx* ctx, const void* d_image, uint64_t n_pages, uint32_t* d_ref, uint64_t* n_mismatch, void* stream,
+                          char* err, size_t errlen) {
+  if (int rc = enter(ctx, err, errlen)) return rc;
+  if (int rc = check_pages(n_pages, d_image, err, errlen)) return rc;
+  if (n_pages && (!d_image || !d_ref)) return fail(err, errlen, GRIT_EINVAL, "null buffer");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  cudaStream_t s = pick(ctx, stream);
+  unsigned long long before = 0, after = 0;
+  GRIT_CUDA(cudaMemcpyAsync(&before, &ctx->d_cnt->dup_mismatch, sizeof before, cudaMemcpyDeviceToHost, s));
+  GRIT_CUDA(launch_verify_dups(ctx->geom, d_image, n_pages, d_ref, ctx->d_cnt, s));
+  ctx->launches++;
+  GRIT_CUDA(cudaMemcpyAsync(&after, &ctx->d_cnt->dup_mismatch, sizeof after, cudaMemcpyDeviceToHost, s));
+  GRIT_CUDA(cudaStreamSynchronize(s));
+  if (n_mismatch) *n_mismatch = after - before;
+  return GRIT_OK;
 }
 
 int grit_compact_pages(grit_ctx* ctx, const void* d_image, uint64_t n_pages, uint32_t* d_ref, void* d_packed,
@@ -387,7 +422,7 @@ int grit_pack_buffer(grit_ctx* ctx, const void* d_image, uint64_t n_pages, const
   ctx->through_image = nullptr;
   if (n_pages && d_packed) {
     if (full && write_through_pack()) path = kThrough;  // the sample decides on the device which K1 variant runs
-    if (onepass_pack()) {  // a different kernel sequence: the host needs the sample's answer, at the price of a sync
+    if (onepass_pack() && !ctx->verify_dup_bytes) {  // a different kernel sequence: the host needs the sample's answer, at the price of a sync
       path = kOnepass;
       if (full && write_through_pack()) {
         GRIT_CUDA(launch_probe_dense(d_image, n_pages, ctx->d_cnt, s));
@@ -419,6 +454,10 @@ int grit_pack_buffer(grit_ctx* ctx, const void* d_image, uint64_t n_pages, const
     }
     GRIT_CUDA(cudaEventRecord(ctx->evA, s));
     if (int rc = dedup_async(ctx, n_pages, d_crc, d_hash, d_ref, parent, peers, n_peers, s, err, errlen)) return rc;
+    if (ctx->verify_dup_bytes) {  // references within the image are checked byte for byte; a mismatch is stored after all
+      GRIT_CUDA(launch_verify_dups(ctx->geom, d_image, n_pages, d_ref, ctx->d_cnt, s));
+      ctx->launches++;
+    }
     GRIT_CUDA(cudaEventRecord(ctx->evB, s));
     staged = true;
     if (int rc = compact_async(ctx, d_image, n_pages, d_ref, d_packed, capacity_pages, 0, s, err, errlen)) return rc;

@@ -26,6 +26,7 @@ struct grit_ctx {
   unsigned long long* d_status = nullptr;
   uint64_t status_cap = 0;
   uint64_t launches = 0;
+  bool verify_dup_bytes = false;  // grit_ctx_set_option
   std::mutex mu;
   // the last write-through K1 on this context: K3 on the same image and packed buffer leaves pages in place
   const void* through_image = nullptr;

@@ -583,6 +583,31 @@ k_resolve(DedupTable t, uint64_t page0, uint64_t page1, const uint32_t* __restri
   }
 }
 
+// Optional check between K2 and K3 (grit_ctx_set_option "verify_dup_bytes"): a page that K2 turned into a reference to
+// an earlier page of the same image on the strength of its 96-bit key (hash64, CRC-32C) is compared with that page
+// byte for byte; if they differ it is stored after all.  One warp per duplicate, 2 x 4 KiB read.
+__global__ void __launch_bounds__(256)
+k_verify_dups(const uint4* __restrict__ image, uint64_t n_pages, uint32_t* __restrict__ ref, DevCounters* __restrict__ cnt) {
+  const uint32_t lane = threadIdx.x & 31;
+  const uint64_t warps = (uint64_t)gridDim.x * (blockDim.x >> 5);
+  for (uint64_t p = (uint64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); p < n_pages; p += warps) {
+    const uint32_t r = ref[p];
+    if ((r >> 29) != 2u) continue;
+    const uint64_t q = r & 0x1FFFFFFFu;
+    const uint4 *a = image + p * 256 + lane, *b = image + q * 256 + lane;
+    uint32_t diff = 0;
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+      const uint4 x = ldg_stream(a + 32 * j), y = ldg_stream(b + 32 * j);
+      diff |= (x.x ^ y.x) | (x.y ^ y.y) | (x.z ^ y.z) | (x.w ^ y.w);
+    }
+    if (__any_sync(0xFFFFFFFFu, diff != 0) && lane == 0) {
+      ref[p] = kRefKeep;
+      atomicAdd(&cnt->dup_mismatch, 1ull);
+    }
+  }
+}
+
 // ------------------------------------------------------------------ K3 compact
 // Single pass: per 256-page tile, ballot-count the pages to keep, get the tile's
 // exclusive prefix by decoupled look-back over the tile status words, assign
@@ -1376,6 +1401,13 @@ cudaError_t launch_resolve(const LaunchGeom& g, DedupTable t, uint64_t page0, ui
   if (page1 <= page0) return cudaSuccess;
   k_resolve<<<grid_for(g, page1 - page0, 256, 8), 256, 0, s>>>(
       t, page0, page1, d_crc, reinterpret_cast<const unsigned long long*>(d_hash), d_ref, crcs, d_cnt);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_verify_dups(const LaunchGeom& g, const void* d_image, uint64_t n_pages, uint32_t* d_ref, DevCounters* d_cnt,
+                               cudaStream_t s) {
+  if (!n_pages) return cudaSuccess;
+  k_verify_dups<<<grid_for(g, n_pages, 64, 8), 256, 0, s>>>(static_cast<const uint4*>(d_image), n_pages, d_ref, d_cnt);
   return cudaGetLastError();
 }
 

@@ -88,6 +88,7 @@ struct DevCounters {
   unsigned int dense_hint;            // 1: the sampled pages held no zero page and K1 wrote the pages through
   unsigned int n_nonkeep;             // K2 since that K1: pages that became DUP / PARENT / PEER references
   unsigned long long through_from;    // first page K1 wrote through (pages in front of it were only analysed)
+  unsigned long long dup_mismatch;    // verify_dup_bytes: duplicates by key whose bytes differed (since the context was made)
 };
 
 struct LaunchGeom {
@@ -104,6 +105,8 @@ cudaError_t launch_table_insert(const LaunchGeom& g, DedupTable t, const uint64_
 cudaError_t launch_table_probe_lists(const LaunchGeom& g, DedupTable t, const ProbeLists& lists, cudaStream_t s);
 cudaError_t launch_resolve(const LaunchGeom& g, DedupTable t, uint64_t page0, uint64_t page1, const uint32_t* d_crc,
                            const uint64_t* d_hash, uint32_t* d_ref, PeerCrcs crcs, DevCounters* d_cnt, cudaStream_t s);
+cudaError_t launch_verify_dups(const LaunchGeom& g, const void* d_image, uint64_t n_pages, uint32_t* d_ref, DevCounters* d_cnt,
+                               cudaStream_t s);
 cudaError_t launch_compact(const LaunchGeom& g, const void* d_image, uint64_t n_pages, uint32_t* d_ref,
                            void* d_packed, uint64_t capacity_pages, uint64_t slot_base, bool chained,
                            unsigned long long* d_tile_status, DevCounters* d_cnt, cudaStream_t s,

@@ -128,6 +128,14 @@ int grit_warmup(int device);
 /* Number of kernels this context has launched (bench.py's gpu_launches). */
 uint64_t grit_ctx_launches(const grit_ctx *ctx);
 
+/* Options of a context, by name.  "verify_dup_bytes" (0 / 1, default 0): grit_pack_buffer compares every page that
+ * became a reference to an earlier page of the same image -- on the strength of the 96-bit key (hash64, CRC-32C) -- with
+ * that page byte for byte before it drops it, and stores it after all if the bytes differ; grit_ctx_dup_mismatches
+ * counts such pages since the context was made.  References to a parent or to a lower rank cannot be checked this way
+ * (only their tables are there at pack time).  Unknown names return GRIT_EINVAL.  No reference counterpart. */
+int grit_ctx_set_option(grit_ctx *ctx, const char *name, uint64_t value);
+uint64_t grit_ctx_dup_mismatches(grit_ctx *ctx);
+
 /* ---- page kernels on device buffers ----------------------------------
  * These have no reference counterpart: copy.go:79 (io.Copy) moves opaque
  * bytes.  They are the new work north_star places behind TransferData. */
@@ -163,6 +171,14 @@ int grit_dedup_pages(grit_ctx *ctx, uint64_t n_pages, const uint32_t *d_crc,
                      const uint64_t *d_hash, uint32_t *d_ref,
                      const grit_table *parent, const grit_table *peers,
                      uint32_t n_peers, void *stream, char *err, size_t errlen);
+
+/* Between K2 and K3, for callers who want more than the 96-bit key: every page K2 turned into a reference to an earlier
+ * page of the same image (GRIT_KIND_DUP) is compared with that page byte for byte; where the bytes differ d_ref[p] goes
+ * back to 0xFFFFFFFE (store it) and *n_mismatch counts it.  grit_pack_buffer does this itself when the context option
+ * "verify_dup_bytes" is set.  No reference counterpart. */
+int grit_verify_dup_pages(grit_ctx *ctx, const void *d_image, uint64_t n_pages,
+                          uint32_t *d_ref, uint64_t *n_mismatch, void *stream,
+                          char *err, size_t errlen);
 
 /* K3: stream compaction.  Pages marked 0xFFFFFFFE get consecutive slots
  * slot_base, slot_base+1, ... in page order (warp ballot + decoupled look-back

@@ -91,3 +91,10 @@ func CreateSentinelFile(dir, fileName string) error {
 	}
 	return nil
 }
+
+// Warmup brings the CUDA runtime up on a goroutine of its own.  A process's first CUDA call costs 0.3-0.5 s whatever it
+// does: RunCheckpoint calls Warmup before RuntimeCheckpointPod (pkg/gritagent/checkpoint/checkpoint.go:14), so that the
+// cost hides behind the CRIU dump, and RunRestore calls it first thing.
+func Warmup() {
+	go func() { C.grit_warmup(0) }()
+}

@@ -374,3 +374,37 @@ def test_bad_arguments_are_refused_with_a_message(ctx):
     # a device that does not exist
     hnd = C.c_void_p()
     assert lib.grit_ctx_create(99, C.byref(hnd), err, len(err)) == _lib.EINVAL and b"out of range" in err.value
+
+
+def test_duplicates_can_be_checked_byte_for_byte(ctx, oracle):
+    """The 96-bit key (hash64, CRC-32C) decides what is a duplicate; a caller who wants more can have every DUP
+    reference compared with its owner's bytes (grit_verify_dup_pages, or the context option "verify_dup_bytes").  A
+    real key collision cannot be made, so one is staged: after K2 has decided, a duplicate's bytes are changed."""
+    n = 5000
+    img = oracle.synth_image(n, 99, pct_zero=5, pct_dup=40, dup_pool=3)
+    d = torch.from_numpy(img).cuda()
+    crc, h, ref = ctx.analyze(d)
+    ctx.dedup(crc, h, ref)
+    kinds = (ref >> 29) & 7
+    dups = torch.nonzero(kinds == 2).flatten()
+    assert dups.numel() > 1000
+    assert ctx.verify_dups(d, ref) == 0 and int(((ref >> 29) & 7 == 2).sum()) == dups.numel()     # honest duplicates stay
+    victims = dups[[10, 500, dups.numel() - 1]]
+    for p in victims.tolist():
+        d[p * PAGE + 77] ^= 1                                                                  # one bit, somewhere
+    assert ctx.verify_dups(d, ref) == 3
+    assert all(int(ref[p]) & 0xFFFFFFFF == 0xFFFFFFFE for p in victims.tolist())
+    packed = torch.empty(n * PAGE, dtype=torch.uint8, device="cuda")
+    stored = ctx.compact(d, ref, packed)
+    out, st = ctx.restore(packed[: stored * PAGE], ref, crc, verify=False)     # the CRCs are those of the original bytes
+    assert torch.equal(out, d)
+    # the context option: grit_pack_buffer checks by itself (nothing to find in an honest image, same result as without)
+    ctx.set_option("verify_dup_bytes", 1)
+    try:
+        r = ctx.pack(torch.from_numpy(img).cuda())
+        o = oracle.pack(img)
+        assert np.array_equal(r["ref"].cpu().numpy().view(np.uint32), o["ref"]) and ctx.dup_mismatches == 3
+    finally:
+        ctx.set_option("verify_dup_bytes", 0)
+    with pytest.raises(Exception):
+        ctx.set_option("no_such_option", 1)
