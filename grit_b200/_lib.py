@@ -46,7 +46,8 @@ class RestoreStats(C.Structure):
 class Opts(C.Structure):
     _fields_ = [("struct_size", C.c_uint32), ("device", C.c_int32), ("verify", C.c_uint32),
                 ("io_threads", C.c_uint32), ("chunk_bytes", C.c_uint64), ("parent_dir", C.c_char_p),
-                ("n_peers", C.c_uint32), ("peer_tables", C.POINTER(Table)), ("peer_dirs", C.POINTER(C.c_char_p))]
+                ("n_peers", C.c_uint32), ("peer_tables", C.POINTER(Table)), ("peer_dirs", C.POINTER(C.c_char_p)),
+                ("comm", C.c_void_p)]
 
 
 class Stats(C.Structure):

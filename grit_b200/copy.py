@@ -16,7 +16,7 @@ from ._lib import GritError, Opts, Stats
 UPLOAD, DOWNLOAD = "upload", "download"
 
 
-def _opts(device=0, verify=True, io_threads=0, chunk_bytes=0, parent_dir=None, peers=()):
+def _opts(device=0, verify=True, io_threads=0, chunk_bytes=0, parent_dir=None, peers=(), comm=None, peer_dirs=()):
     """peers: [(hash64 array, crc32c array, packed_dir)] of the ranks below this one, in rank order -- numpy arrays
     (uint64 / uint32), e.g. from grit_b200.dist.all_gather_tables or read_tables() of the lower ranks' directories."""
     import numpy as np
@@ -39,6 +39,12 @@ def _opts(device=0, verify=True, io_threads=0, chunk_bytes=0, parent_dir=None, p
             dirs[i] = os.fsencode(d)
         o.n_peers, o.peer_tables, o.peer_dirs = len(peers), tabs, dirs
         o._keep = (keep, tabs, dirs)
+    if comm is not None:
+        # a ranked upload (grit_b200.dist.Comm): the tables travel over NCCL inside the library; peer_dirs names the
+        # packed directories of the ranks below this one, in rank order
+        dirs = (C.c_char_p * max(len(peer_dirs), 1))(*[os.fsencode(d) for d in peer_dirs])
+        o.comm, o.n_peers, o.peer_dirs = comm.handle, len(peer_dirs), dirs
+        o._keep = (dirs, comm)
     return o
 
 

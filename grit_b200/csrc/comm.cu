@@ -106,6 +106,51 @@ struct grit_comm {
   uint64_t exchanges = 0;
 };
 
+namespace grit {
+
+grit_ctx* comm_context(grit_comm* c) { return c ? c->ctx : nullptr; }
+int comm_rank_of(const grit_comm* c) { return c ? c->rank : -1; }
+
+int comm_gather_tables(grit_comm* c, const uint64_t* d_hash, const uint32_t* d_crc, uint64_t n_pages, grit_table* lower,
+                       char* err, size_t errlen) {
+  grit_ctx* ctx = c->ctx;
+  const int W = c->world;
+  cudaStream_t cs = c->cs;
+  GRIT_CUDA(cudaSetDevice(ctx->device));
+  GRIT_CUDA(cudaMemcpyAsync(c->d_counts + c->rank, &n_pages, sizeof(uint64_t), cudaMemcpyHostToDevice, cs));
+  GRIT_NCCL(g_nccl.AllGather(c->d_counts + c->rank, c->d_counts, 1, ncclUint64, c->nccl, cs));
+  GRIT_CUDA(cudaMemcpyAsync(c->h_counts, c->d_counts, W * sizeof(uint64_t), cudaMemcpyDeviceToHost, cs));
+  GRIT_CUDA(cudaStreamSynchronize(cs));
+  uint64_t L = 1;
+  for (int r = 0; r < W; r++) L = std::max<uint64_t>(L, c->h_counts[r]);
+  if (L > GRIT_MAX_PAGES) return fail(err, errlen, GRIT_EINVAL, "a rank's image exceeds GRIT_MAX_PAGES");
+  void *ph = nullptr, *pc = nullptr, *pp = nullptr;
+  if (int rc = ctx_dev(ctx, kDevCommHash, (uint64_t)W * L * 8, &ph, err, errlen)) return rc;
+  if (int rc = ctx_dev(ctx, kDevCommCrc, (uint64_t)W * L * 4, &pc, err, errlen)) return rc;
+  if (int rc = ctx_dev(ctx, kDevCommPad, L * 12, &pp, err, errlen)) return rc;
+  uint64_t* pad_hash = static_cast<uint64_t*>(pp);
+  uint32_t* pad_crc = reinterpret_cast<uint32_t*>(pad_hash + L);
+  GRIT_CUDA(cudaMemsetAsync(pp, 0, L * 12, cs));  // every rank sends L entries: zero padding behind its own (hash64 is never 0)
+  if (n_pages) {
+    GRIT_CUDA(cudaMemcpyAsync(pad_hash, d_hash, n_pages * 8, cudaMemcpyDeviceToDevice, cs));
+    GRIT_CUDA(cudaMemcpyAsync(pad_crc, d_crc, n_pages * 4, cudaMemcpyDeviceToDevice, cs));
+  }
+  GRIT_NCCL(g_nccl.GroupStart());
+  GRIT_NCCL(g_nccl.AllGather(pad_hash, ph, L, ncclUint64, c->nccl, cs));
+  GRIT_NCCL(g_nccl.AllGather(pad_crc, pc, L, ncclUint32, c->nccl, cs));
+  GRIT_NCCL(g_nccl.GroupEnd());
+  GRIT_CUDA(cudaStreamSynchronize(cs));
+  for (int r = 0; r < c->rank; r++) {
+    lower[r].hash = static_cast<const uint64_t*>(ph) + (uint64_t)r * L;
+    lower[r].crc = static_cast<const uint32_t*>(pc) + (uint64_t)r * L;
+    lower[r].n_pages = c->h_counts[r];
+  }
+  c->exchanges++;
+  return GRIT_OK;
+}
+
+}  // namespace grit
+
 extern "C" {
 
 int grit_comm_new_id(void* id, char* err, size_t errlen) {

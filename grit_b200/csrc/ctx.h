@@ -82,6 +82,13 @@ enum DevBuf { kDevIn0 = 0, kDevOut0 = 3, kDevRef = 6, kDevCrc, kDevHash, kDevPar
               kDevPeerHash0 = 18 /* ..25 */, kDevPeerCrc0 = 26 /* ..33 */, kDevCommHash = 34, kDevCommCrc, kDevCommPad, kDevROutX0 = 37 /* ..41 */ };
 enum PinBuf { kPinIn0 = 0, kPinOut0 = 3, kPinCounts = 6, kPinMeta0 = 7, kPinRStageOut0 = 10, kPinRStageIn0 = 13 /* ..15 */,
               kPinRStageOutX0 = 16 /* ..20 */ };
+// comm.cu, for the directory packer: the context a communicator lives on, its rank, and a whole-table exchange --
+// every rank's (hash64, crc) arrays gathered into device buffers of the context; lower[r] (r < rank) receives DEVICE
+// pointers to rank r's tables (valid until the next exchange on this context).  Collective; synchronises.
+grit_ctx* comm_context(grit_comm* c);
+int comm_rank_of(const grit_comm* c);
+int comm_gather_tables(grit_comm* c, const uint64_t* d_hash, const uint32_t* d_crc, uint64_t n_pages, grit_table* lower,
+                       char* err, size_t errlen);
 bool write_through_pack();  // false with GRITPACK_WRITE_THROUGH=0
 bool onepass_pack();  // true with GRITPACK_ONEPASS=1: grit_pack_buffer packs non-dense images with the single-pass kernel
 

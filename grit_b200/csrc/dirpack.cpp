@@ -567,6 +567,7 @@ struct Opts {
   uint32_t n_peers = 0;
   const grit_table* peer_tables = nullptr;
   std::vector<std::string> peer_dirs;
+  grit_comm* comm = nullptr;  // ranked pack: the tables come over NCCL instead of through peer_tables
   // Chunks of 1/128 of the image, 4 to 16 MiB.  The pinned staging is six chunks, and pinning memory costs about
   // 0.5 ms per MiB (cudaHostAlloc, and again to free): with 64 MiB chunks that was 0.2-0.4 s per call for nothing,
   // since the I/O threads split a chunk among themselves whatever its size and a PCIe copy of 4 MiB is at full rate.
@@ -587,11 +588,14 @@ Opts read_opts(const grit_opts* o) {
   if (const char* e = getenv("GRITPACK_LANES")) r.lanes = std::max(1, atoi(e));
   if (o->chunk_bytes >= (1u << 20)) r.chunk_pages = o->chunk_bytes / kPage;
   if (o->parent_dir) r.parent = o->parent_dir;
-  if (o->struct_size >= sizeof(grit_opts) && o->n_peers && o->peer_tables && o->peer_dirs) {
-    r.n_peers = o->n_peers;
-    r.peer_tables = o->peer_tables;
+  const bool has_comm = o->struct_size >= offsetof(grit_opts, comm) + sizeof(o->comm) && o->comm;
+  if (o->struct_size >= offsetof(grit_opts, peer_dirs) + sizeof(o->peer_dirs) && o->n_peers && o->peer_dirs &&
+      (o->peer_tables || has_comm)) {
+    r.n_peers = has_comm ? 0 : o->n_peers;
+    r.peer_tables = has_comm ? nullptr : o->peer_tables;
     for (uint32_t i = 0; i < o->n_peers; i++) r.peer_dirs.emplace_back(o->peer_dirs[i] ? o->peer_dirs[i] : "");
   }
+  if (has_comm) r.comm = o->comm;
   return r;
 }
 
@@ -813,18 +817,64 @@ int grit_pack_dir(const char* src_dir, const char* dst_dir, const grit_opts* opt
   IoPool pool(o.io_threads);
 
   ph.mark("walk+open");
-  CtxGuard cg;
-  if (int rc = grit_ctx_create(o.device, &cg.ctx, err, errlen)) return rc;
-  grit_ctx* ctx = cg.ctx;
+  CtxGuard cg;  // owns the context unless a communicator brings its own
+  grit_ctx* ctx = o.comm ? comm_context(o.comm) : nullptr;
+  if (!ctx) {
+    if (int rc = grit_ctx_create(o.device, &cg.ctx, err, errlen)) return rc;
+    ctx = cg.ctx;
+  }
   ph.mark("ctx");
   std::vector<uint32_t> ref(std::max<uint64_t>(m.n_pages, 1)), crc(std::max<uint64_t>(m.n_pages, 1));
   std::vector<uint64_t> hash(std::max<uint64_t>(m.n_pages, 1));
   grit_pack_stats ps{};
+  // A ranked pack (grit_opts.comm): the tree goes through the GPU twice.  The first pass only analyses (K1 of every
+  // chunk), then the ranks exchange their tables over NCCL, then the usual pass packs against the lower ranks' tables,
+  // which never leave the device.  The host link carries the tree twice; the PV, usually the slower of the two, stores
+  // what no lower rank stores.
+  grit_table lower[GRIT_MAX_PEERS] = {};
+  const grit_table* peer_tables = o.peer_tables;
+  uint32_t n_peer_tables = o.n_peers;
+  bool peers_on_device = false;
+  if (o.comm) {
+    const int rank = comm_rank_of(o.comm);
+    if ((int)o.peer_dirs.size() != rank)
+      return fail(err, errlen, GRIT_EINVAL, "rank %d must name the packed directories of the %d ranks below it (peer_dirs)", rank, rank);
+    double h2d_first = 0;
+    {
+      PackStream pa(ctx, m.n_pages, chunk_pages);
+      pa.set_analyze_only();
+      if (int rc = pa.begin(nullptr, err, errlen)) return rc;
+      if (m.n_pages)
+        if (int rc = pa.alloc_staging(true, false, err, errlen)) return rc;
+      const uint64_t cp = pa.chunk_pages(), n_chunks = (m.n_pages + cp - 1) / cp;
+      for (uint64_t i = 0; i < n_chunks; i++) {
+        const uint64_t p0 = i * cp, p1 = std::min(m.n_pages, p0 + cp);
+        if (int rc = pa.wait_in_free(i, err, errlen)) return rc;
+        char* buf = static_cast<char*>(pa.in_buffer(i));
+        std::vector<Piece> pieces;
+        pieces_for(files, p0, p1, buf, piece_bytes_for(cp, o.io_threads), &pieces);
+        zero_tails(files, p0, p1, buf);
+        if (int rc = for_pieces(&pool, pieces, &msg, [&](const Piece& p, std::string* e) { read_piece(src, p, e); }))
+          return fail(err, errlen, rc, "%s", msg.c_str());
+        if (int rc = pa.submit(i, buf, p1 - p0, err, errlen)) return rc;
+      }
+      if (n_chunks)
+        if (int rc = pa.wait_chunk(n_chunks - 1, err, errlen)) return rc;
+      GRIT_CUDA(cudaStreamSynchronize(ctx->stream));
+      if (int rc = comm_gather_tables(o.comm, pa.device_hash(), pa.device_crc(), m.n_pages, lower, err, errlen)) return rc;
+      h2d_first = pa.h2d_bytes;
+    }
+    st.h2d_bytes += h2d_first;
+    peer_tables = lower;
+    n_peer_tables = (uint32_t)rank;
+    peers_on_device = true;
+    ph.mark("analyze pass + exchange");
+  }
   {
     PackStream pk(ctx, m.n_pages, chunk_pages);
     pk.set_outputs(ref.data(), crc.data(), hash.data());
-    if (o.n_peers > GRIT_MAX_PEERS) return fail(err, errlen, GRIT_EINVAL, "n_peers %u > %u", o.n_peers, GRIT_MAX_PEERS);
-    if (int rc = pk.begin(parent.n_pages ? &parent : nullptr, err, errlen, o.peer_tables, o.n_peers)) return rc;
+    if (n_peer_tables > GRIT_MAX_PEERS) return fail(err, errlen, GRIT_EINVAL, "n_peers %u > %u", n_peer_tables, GRIT_MAX_PEERS);
+    if (int rc = pk.begin(parent.n_pages ? &parent : nullptr, err, errlen, peer_tables, n_peer_tables, peers_on_device)) return rc;
     if (m.n_pages)
       if (int rc = pk.alloc_staging(true, true, err, errlen)) return rc;
     const uint64_t cp = pk.chunk_pages(), n_chunks = (m.n_pages + cp - 1) / cp;
@@ -912,10 +962,10 @@ int grit_pack_dir(const char* src_dir, const char* dst_dir, const grit_opts* opt
     if (rc) return rc;
     ph.mark("stream");
     if ((rc = pk.finish(&ps, err, errlen))) return rc;
-    st.h2d_bytes = pk.h2d_bytes;
+    st.h2d_bytes += pk.h2d_bytes;
     st.d2h_bytes = pk.d2h_bytes;
   }
-  if (ps.n_peer && !o.n_peers) return fail(err, errlen, GRIT_EINVAL, "internal: peer references in a single-rank pack");
+  if (ps.n_peer && !n_peer_tables) return fail(err, errlen, GRIT_EINVAL, "internal: peer references in a single-rank pack");
   m.peers = o.peer_dirs;
   ph.mark("finish+free");
   m.n_slots = ps.n_data;

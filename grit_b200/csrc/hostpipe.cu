@@ -57,7 +57,8 @@ PackStream::~PackStream() {
   // the buffers belong to the context's cache and stay for the next call
 }
 
-int PackStream::begin(const grit_table* parent, char* err, size_t errlen, const grit_table* peers, uint32_t n_peers) {
+int PackStream::begin(const grit_table* parent, char* err, size_t errlen, const grit_table* peers, uint32_t n_peers,
+                      bool peers_on_device) {
   GRIT_CUDA(cudaSetDevice(ctx_->device));
   if (total_pages_ > GRIT_MAX_PAGES) return fail(err, errlen, GRIT_EINVAL, "image exceeds GRIT_MAX_PAGES");
   const size_t chunk_bytes = chunk_pages_ * kPage;
@@ -103,13 +104,15 @@ int PackStream::begin(const grit_table* parent, char* err, size_t errlen, const 
   }
   for (uint32_t r = 0; r < n_peers; r++) {
     if (!peers[r].n_pages) continue;
-    void *dh = nullptr, *dc = nullptr;  // cached in the context like every other working buffer
-    if (int rc = ctx_dev(ctx_, kDevPeerHash0 + (int)r, peers[r].n_pages * 8, &dh, err, errlen)) return rc;
-    if (int rc = ctx_dev(ctx_, kDevPeerCrc0 + (int)r, peers[r].n_pages * 4, &dc, err, errlen)) return rc;
-    GRIT_CUDA(cudaMemcpyAsync(dh, peers[r].hash, peers[r].n_pages * 8, cudaMemcpyHostToDevice, s));
-    GRIT_CUDA(cudaMemcpyAsync(dc, peers[r].crc, peers[r].n_pages * 4, cudaMemcpyHostToDevice, s));
+    void *dh = const_cast<uint64_t*>(peers[r].hash), *dc = const_cast<uint32_t*>(peers[r].crc);
+    if (!peers_on_device) {  // cached in the context like every other working buffer
+      if (int rc = ctx_dev(ctx_, kDevPeerHash0 + (int)r, peers[r].n_pages * 8, &dh, err, errlen)) return rc;
+      if (int rc = ctx_dev(ctx_, kDevPeerCrc0 + (int)r, peers[r].n_pages * 4, &dc, err, errlen)) return rc;
+      GRIT_CUDA(cudaMemcpyAsync(dh, peers[r].hash, peers[r].n_pages * 8, cudaMemcpyHostToDevice, s));
+      GRIT_CUDA(cudaMemcpyAsync(dc, peers[r].crc, peers[r].n_pages * 4, cudaMemcpyHostToDevice, s));
+      h2d_bytes += peers[r].n_pages * 12.0;
+    }
     crcs_.peer[r].base = static_cast<const uint32_t*>(dc);
-    h2d_bytes += peers[r].n_pages * 12.0;
     GRIT_CUDA(launch_table_insert(ctx_->geom, table_, static_cast<const uint64_t*>(dh), nullptr, peers[r].n_pages, 1 + r, 0, s));
     ctx_->launches++;
   }
@@ -150,6 +153,13 @@ int PackStream::submit(uint64_t i, const void* h_src, uint64_t n_pages, char* er
   if (!timing_started_) {
     GRIT_CUDA(cudaEventRecord(ctx_->ev0, s));
     timing_started_ = true;
+  }
+  if (analyze_only_) {  // first pass of a ranked directory pack: hashes only
+    GRIT_CUDA(launch_analyze(ctx_->geom, ctx_->d_tables, d_in_[b], n_pages, d_crc_ + p0, d_hash_ + p0, d_ref_ + p0, s));
+    ctx_->launches++;
+    GRIT_CUDA(cudaEventRecord(ev_kern_[b], s));
+    pages_done_ += n_pages;
+    return GRIT_OK;
   }
   GRIT_CUDA(cudaMemsetAsync(ctx_->d_status, 0, (n_pages + kCompactTile - 1) / kCompactTile * sizeof(unsigned long long), s));
   GRIT_CUDA(cudaMemsetAsync(&ctx_->d_cnt->ticket, 0, 3 * sizeof(unsigned int), s));  // ticket and its neighbours
@@ -204,6 +214,11 @@ int PackStream::collect_at(uint64_t i, void* h_dst_base, uint64_t capacity_pages
     return fail(err, errlen, GRIT_EINVAL, "packed buffer too small: need more than %llu pages",
                 (unsigned long long)capacity_pages);
   return collect(i, static_cast<char*>(h_dst_base) + slots_done_ * kPage, first_slot, n_out, err, errlen);
+}
+
+int PackStream::wait_chunk(uint64_t i, char* err, size_t errlen) {
+  GRIT_CUDA(cudaEventSynchronize(ev_kern_[i % kPipeDepth]));
+  return GRIT_OK;
 }
 
 int PackStream::wait_out(uint64_t i, char* err, size_t errlen) {

@@ -26,8 +26,15 @@ class PackStream {
   ~PackStream();
   // parent: HOST arrays of the previous checkpoint's per-page hashes, or null
   // peers_host[0..n_peers): HOST tables of the ranks below this one
+  // peers_on_device: the peers' tables are DEVICE arrays already (gathered by a grit_comm), nothing is uploaded
   int begin(const grit_table* parent_host, char* err, size_t errlen, const grit_table* peers_host = nullptr,
-            uint32_t n_peers = 0);
+            uint32_t n_peers = 0, bool peers_on_device = false);
+  // A stream that only analyses (K1 of every chunk into the whole-image arrays, nothing stored or downloaded): the
+  // first pass of a ranked directory pack, whose tables the ranks exchange before the second, packing pass.
+  void set_analyze_only() { analyze_only_ = true; }
+  int wait_chunk(uint64_t i, char* err, size_t errlen);  // the kernels of chunk i are done
+  const uint64_t* device_hash() const { return d_hash_; }
+  const uint32_t* device_crc() const { return d_crc_; }
   // pinned staging buffers, one per chunk in flight, for callers without pinned memory
   int alloc_staging(bool in, bool out, char* err, size_t errlen);
   // pinned staging buffer for chunk i (valid between submit-ready and the H2D of chunk i)
@@ -76,7 +83,7 @@ class PackStream {
   uint64_t chunk_page0_[kPipeDepth] = {};
   DedupTable table_{};
   PeerCrcs crcs_{};
-  bool timing_started_ = false;
+  bool timing_started_ = false, analyze_only_ = false;
 };
 
 // Where a streamed restore reads the packed pages from and delivers the image to.

@@ -88,6 +88,14 @@ typedef struct grit_opts {
   uint32_t n_peers;              /* 0..GRIT_MAX_PEERS                              */
   const grit_table *peer_tables; /* [n_peers]                                      */
   const char *const *peer_dirs;  /* [n_peers]                                      */
+  /* grit_pack_dir of one rank of a job, all ranks at once (collective): instead of
+   * peer_tables, a communicator made with grit_comm_create.  The call runs on the
+   * communicator's context (`device` is ignored); the tree goes through the GPU
+   * twice -- analysed, the tables exchanged over NCCL, then packed against the lower
+   * ranks' tables, which never leave the device -- so the host link carries it
+   * twice and the PV stores what no lower rank stores.  n_peers / peer_dirs still
+   * name the packed directories of the ranks below this one (n_peers = rank).   */
+  struct grit_comm *comm;
 } grit_opts;
 
 typedef struct grit_stats {

@@ -99,6 +99,59 @@ def _worker(rank, world, port):
         dist.destroy_process_group()
 
 
+def _dir_worker(rank, world, port, root):
+    sys.path.insert(0, HERE)
+    sys.path.insert(0, os.path.dirname(HERE))
+    import oracle_lib as O
+    from grit_b200 import copy, dist as gdist
+    from grit_b200.buffers import Context
+    from helpers import tree_snapshot
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        ctx = Context(rank)
+        comm = gdist.Comm.from_torch_distributed(ctx)
+        src = os.path.join(root, f"host{rank}", "main", "checkpoint")
+        os.makedirs(src)
+        with open(os.path.join(src, "pages-1.img"), "wb") as f:            # replicated weights: the same on every rank
+            f.write(O.synth_image(20_000, 0xBA5E, pct_zero=0, pct_dup=0).tobytes())
+        with open(os.path.join(src, "pages-2.img"), "wb") as f:
+            f.write(O.synth_image(3000 + 500 * rank, 700 + rank, pct_zero=10, pct_dup=10, dup_pool=4).tobytes())
+        with open(os.path.join(src, "inventory.img"), "wb") as f:
+            f.write(bytes([rank]) * 123)
+        pvs = [os.path.join(root, "pv", f"ckpt-rank{q}") for q in range(world)]
+        st = copy.TransferData(os.path.join(root, f"host{rank}"), pvs[rank], copy.UPLOAD, comm=comm, peer_dirs=pvs[:rank],
+                               chunk_bytes=8 << 20)
+        if rank == 0:
+            assert st["n_peer"] == 0
+        else:
+            assert st["n_peer"] >= 20_000 and st["n_data"] < 4000 + 500 * rank
+        dist.barrier()                                                      # every rank's directory is complete
+        back = os.path.join(root, f"back{rank}")
+        rs = copy.TransferData(pvs[rank], back, copy.DOWNLOAD, device=rank)
+        assert rs["n_bad"] == 0 and tree_snapshot(back) == tree_snapshot(os.path.join(root, f"host{rank}"))
+        # the same tree packed with the lower ranks' tables read from their directories gives the same page map
+        again = os.path.join(root, "pv", f"again-rank{rank}")
+        peers = [copy.read_tables(pvs[q]) + (pvs[q],) for q in range(rank)]
+        copy.TransferData(os.path.join(root, f"host{rank}"), again, copy.UPLOAD, device=rank, peers=peers, chunk_bytes=8 << 20)
+        assert open(os.path.join(again, "pagemap.bin"), "rb").read() == open(os.path.join(pvs[rank], "pagemap.bin"), "rb").read()
+        dist.barrier()
+        comm.close()
+        ctx.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_ranked_directory_pack_over_nccl(tmp_path):
+    """grit_opts.comm: every rank packs its own tree at the same time; the tables cross NCCL inside the library after a
+    first, analysing pass over the tree; the page map equals the one a pack against the lower ranks' hashes.bin gives."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs at least 2 GPUs")
+    world = min(torch.cuda.device_count(), 4)
+    mp.spawn(_dir_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+
+
 def test_cross_rank_pack_and_restore_over_nccl():
     if torch.cuda.device_count() < 2:
         pytest.skip("needs at least 2 GPUs")
