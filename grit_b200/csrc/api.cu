@@ -104,6 +104,27 @@ int dedup_views_async(grit_ctx* ctx, uint64_t n_pages, const uint32_t* d_crc, co
                       const PeerCrcs& crcs, const ProbeLists& lists, cudaStream_t s, char* err, size_t errlen,
                       cudaEvent_t lists_ready) {
   DedupTable t{};
+  bool peers_on = false;
+  for (int o = 1; o < 9; o++) peers_on = peers_on || (lists.n[o] && lists.hash[o]);
+  if (!peers_on && lists.n[0] && lists.hash[0] && lists.hash[0].stride == 0 && crcs.parent) {
+    // An incremental pack: most pages are the parent's.  One table is built from the parent, and a page whose hash
+    // is found there is settled after one read; the rest (the dirtied pages) meet in a second table.  Both are sized
+    // for the worst case, so an unrelated parent costs time and never a crowded table.
+    uint64_t cap_a = 1024, cap_b = 1024;
+    while (cap_a < 2 * lists.n[0]) cap_a <<= 1;
+    while (cap_b < 2 * n_pages) cap_b <<= 1;
+    if (int rc = ensure_table(ctx, (cap_a + cap_b) / 2, &t, err, errlen)) return rc;
+    const DedupTable ta{t.slots, cap_a - 1}, tb{t.slots + cap_a, cap_b - 1};
+    GRIT_CUDA(launch_table_clear(ctx->geom, DedupTable{t.slots, cap_a + cap_b - 1}, s));
+    if (lists_ready) GRIT_CUDA(cudaStreamWaitEvent(s, lists_ready, 0));
+    GRIT_CUDA(launch_table_insert(ctx->geom, ta, reinterpret_cast<const uint64_t*>(lists.hash[0].base), nullptr, lists.n[0], 0,
+                                  0, s));
+    GRIT_CUDA(launch_resolve_parent(ctx->geom, ta, n_pages, d_crc, d_hash, d_ref, crcs.parent, ctx->d_cnt, s));
+    GRIT_CUDA(launch_table_insert(ctx->geom, tb, d_hash, d_ref, n_pages, kOriginSelf, 0, s, true));
+    GRIT_CUDA(launch_resolve(ctx->geom, tb, 0, n_pages, d_crc, d_hash, d_ref, crcs, ctx->d_cnt, s, true));
+    ctx->launches += 5;
+    return GRIT_OK;
+  }
   if (int rc = ensure_table(ctx, n_pages, &t, err, errlen)) return rc;
   GRIT_CUDA(launch_table_clear(ctx->geom, t, s));
   ctx->launches++;

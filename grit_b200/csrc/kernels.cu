@@ -512,13 +512,16 @@ k_table_clear(DedupTable t) {
     stg_stream(w + i, make_uint4(0u, 0u, 0xFFFFFFFFu, 0u));
 }
 
+// One item per thread and step: several chains in flight per thread (batches of 2, 4, 8 were tried) only slow these
+// kernels down -- at full occupancy the memory system is already saturated with scattered 32-byte accesses.
 __global__ void __launch_bounds__(256)
 k_table_insert(DedupTable t, const unsigned long long* __restrict__ hash, const uint32_t* __restrict__ ref,
-               uint64_t n, uint32_t origin, uint64_t index_base) {
+               uint64_t n, uint32_t origin, uint64_t index_base, bool pending_only) {
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
        i += (uint64_t)gridDim.x * blockDim.x) {
-    if (ref && ref[i] == 0u) continue;  // zero pages never enter the table
+    if (ref && (pending_only ? ref[i] != kRefPending : ref[i] == 0u)) continue;  // zero pages never enter the table
     const unsigned long long h = hash[i];
+    if (h == 0ull) continue;  // hash64 is never 0: a damaged hashes.bin must not claim the empty key
     const uint32_t v = origin << 26 | (uint32_t)(index_base + i);
     for (uint64_t s = table_home(h, t.mask);; s = (s + 1) & t.mask) {
       unsigned long long k = t.slots[s].key;
@@ -533,9 +536,7 @@ k_table_insert(DedupTable t, const unsigned long long* __restrict__ hash, const 
   }
 }
 
-// Other images' hashes against a table that already holds this image's: a hit lowers the owner,
-// a miss touches nothing, so the table stays the size of this image however many peers there are.
-// The parent and every lower rank are probed in one launch: blockIdx.y is the origin.
+// Lowers the owner of every key of THIS image's table that one of the other images (parent, lower ranks) holds too.
 __global__ void __launch_bounds__(256)
 k_table_probe_lists(DedupTable t, ProbeLists lists) {
   const uint32_t origin = blockIdx.y;
@@ -557,13 +558,47 @@ k_table_probe_lists(DedupTable t, ProbeLists lists) {
   }
 }
 
+// K2 of an incremental pack (a parent and no peers).  The table holds the PARENT's pages alone, and a page of this
+// image that finds its hash there is settled after that one read: the parent is origin 0, so its page owns the hash,
+// and the page here is a PARENT reference when the CRCs agree and a stored page when they do not (pages never refer
+// to each other past a differing owner).  Only the pages whose hash the parent does not hold are left kRefPending;
+// they go into a second table (k_table_insert pending_only) and through k_resolve(pending_only), which is the
+// general K2 on the few dirtied pages.  An unchanged page costs one table read instead of an insert, a probe and a
+// lookup.
 __global__ void __launch_bounds__(256)
-k_resolve(DedupTable t, uint64_t page0, uint64_t page1, const uint32_t* __restrict__ crc,
-          const unsigned long long* __restrict__ hash, uint32_t* __restrict__ ref, PeerCrcs crcs, DevCounters* __restrict__ cnt) {
-  for (uint64_t p = page0 + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; p < page1;
-       p += (uint64_t)gridDim.x * blockDim.x) {
+k_resolve_parent(DedupTable t, uint64_t n_pages, const uint32_t* __restrict__ crc,
+                 const unsigned long long* __restrict__ hash, uint32_t* __restrict__ ref, ListView<uint32_t> parent_crc,
+                 DevCounters* __restrict__ cnt) {
+  for (uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n_pages; p += (uint64_t)gridDim.x * blockDim.x) {
     if (ref[p] == 0u) continue;
     const unsigned long long h = hash[p];
+    uint32_t out = h ? kRefPending : kRefKeep;  // K1 never gives hash 0 (the empty key); a caller's own 0 is stored
+    for (uint64_t s = table_home(h, t.mask); h; s = (s + 1) & t.mask) {
+      const ulonglong2 slot = *reinterpret_cast<const ulonglong2*>(&t.slots[s]);  // key and owner in one access
+      if (slot.x == h) {
+        const uint32_t idx = (uint32_t)slot.y & ((1u << 26) - 1);
+        out = parent_crc[idx] == crc[p] ? (3u << 29 | idx) : kRefKeep;
+        break;
+      }
+      if (slot.x == 0ull) break;
+    }
+    ref[p] = out;
+    if (out >> 29 == 3u) atomicAdd(&cnt->n_nonkeep, 1u);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+k_resolve(DedupTable t, uint64_t page0, uint64_t page1, const uint32_t* __restrict__ crc,
+          const unsigned long long* __restrict__ hash, uint32_t* __restrict__ ref, PeerCrcs crcs, DevCounters* __restrict__ cnt,
+          bool pending_only) {
+  for (uint64_t p = page0 + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; p < page1;
+       p += (uint64_t)gridDim.x * blockDim.x) {
+    if (pending_only ? ref[p] != kRefPending : ref[p] == 0u) continue;
+    const unsigned long long h = hash[p];
+    if (h == 0ull) {  // K1 never gives hash 0 (the empty key, not inserted); a caller's own 0 is stored
+      ref[p] = kRefKeep;
+      continue;
+    }
     uint64_t s = table_home(h, t.mask);
     while (t.slots[s].key != h) s = (s + 1) & t.mask;  // inserted by k_table_insert
     const uint32_t v = t.slots[s].val, origin = v >> 26, idx = v & ((1u << 26) - 1);
@@ -650,11 +685,23 @@ k_compact(const uint4* __restrict__ image, uint64_t n_pages, uint32_t* __restric
   const uint64_t ref_base = chained ? cnt->slot_base : slot_base;
   const uint64_t out_base = chained ? 0 : slot_base;
 
+  // The page statistics are summed per block and added once at its end: the counters share a line with the ticket,
+  // and a handful of atomics per tile on that one line would pace an image of short tiles (mostly references).
+  uint32_t sum_zero = 0, sum_keep = 0, sum_dup = 0, sum_par = 0, sum_peer = 0;
   for (;;) {
     if (threadIdx.x == 0) s_tile = atomicAdd(&cnt->ticket, 1u);
     __syncthreads();
     const uint32_t tile = s_tile;
-    if (tile >= n_tiles) return;
+    if (tile >= n_tiles) {
+      if (threadIdx.x == 0) {
+        if (sum_zero) atomicAdd(&cnt->kind[0], (unsigned long long)sum_zero);
+        if (sum_keep) atomicAdd(&cnt->kind[1], (unsigned long long)sum_keep);
+        if (sum_dup) atomicAdd(&cnt->kind[2], (unsigned long long)sum_dup);
+        if (sum_par) atomicAdd(&cnt->kind[3], (unsigned long long)sum_par);
+        if (sum_peer) atomicAdd(&cnt->kind[4], (unsigned long long)sum_peer);
+      }
+      return;
+    }
     const uint64_t p = (uint64_t)tile * kCompactTile + threadIdx.x;
     const uint32_t r = p < n_pages ? ref[p] : 0u;
     const bool keep = r == kRefKeep;
@@ -675,13 +722,11 @@ k_compact(const uint4* __restrict__ image, uint64_t n_pages, uint32_t* __restric
       before += w < (int)warp ? c : 0u;
       total += c;
     }
-    if (threadIdx.x == 0) {
-      if (n_zero) atomicAdd(&cnt->kind[0], (unsigned long long)n_zero);
-      if (total) atomicAdd(&cnt->kind[1], (unsigned long long)total);
-      if (n_dup) atomicAdd(&cnt->kind[2], (unsigned long long)n_dup);
-      if (n_par) atomicAdd(&cnt->kind[3], (unsigned long long)n_par);
-      if (n_peer) atomicAdd(&cnt->kind[4], (unsigned long long)n_peer);
-    }
+    sum_zero += n_zero;
+    sum_keep += total;
+    sum_dup += n_dup;
+    sum_par += n_par;
+    sum_peer += n_peer;
 
     if (warp == 0) {
       if (lane == 0) st_status(&status[tile], (tile == 0 ? kFlagIncl : kFlagAgg) | total);
@@ -1379,10 +1424,19 @@ cudaError_t launch_table_clear(const LaunchGeom& g, DedupTable t, cudaStream_t s
 
 cudaError_t launch_table_insert(const LaunchGeom& g, DedupTable t, const uint64_t* d_hash,
                                 const uint32_t* d_ref_or_null, uint64_t n, uint32_t origin, uint64_t index_base,
-                                cudaStream_t s) {
+                                cudaStream_t s, bool pending_only) {
   if (!n) return cudaSuccess;
   k_table_insert<<<grid_for(g, n, 256, 8), 256, 0, s>>>(
-      t, reinterpret_cast<const unsigned long long*>(d_hash), d_ref_or_null, n, origin, index_base);
+      t, reinterpret_cast<const unsigned long long*>(d_hash), d_ref_or_null, n, origin, index_base, pending_only);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_resolve_parent(const LaunchGeom& g, DedupTable t, uint64_t n_pages, const uint32_t* d_crc,
+                                  const uint64_t* d_hash, uint32_t* d_ref, ListView<uint32_t> parent_crc,
+                                  DevCounters* d_cnt, cudaStream_t s) {
+  if (!n_pages) return cudaSuccess;
+  k_resolve_parent<<<grid_for(g, n_pages, 256, 8), 256, 0, s>>>(
+      t, n_pages, d_crc, reinterpret_cast<const unsigned long long*>(d_hash), d_ref, parent_crc, d_cnt);
   return cudaGetLastError();
 }
 
@@ -1397,10 +1451,11 @@ cudaError_t launch_table_probe_lists(const LaunchGeom& g, DedupTable t, const Pr
 }
 
 cudaError_t launch_resolve(const LaunchGeom& g, DedupTable t, uint64_t page0, uint64_t page1, const uint32_t* d_crc,
-                           const uint64_t* d_hash, uint32_t* d_ref, PeerCrcs crcs, DevCounters* d_cnt, cudaStream_t s) {
+                           const uint64_t* d_hash, uint32_t* d_ref, PeerCrcs crcs, DevCounters* d_cnt, cudaStream_t s,
+                           bool pending_only) {
   if (page1 <= page0) return cudaSuccess;
   k_resolve<<<grid_for(g, page1 - page0, 256, 8), 256, 0, s>>>(
-      t, page0, page1, d_crc, reinterpret_cast<const unsigned long long*>(d_hash), d_ref, crcs, d_cnt);
+      t, page0, page1, d_crc, reinterpret_cast<const unsigned long long*>(d_hash), d_ref, crcs, d_cnt, pending_only);
   return cudaGetLastError();
 }
 

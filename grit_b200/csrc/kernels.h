@@ -101,10 +101,15 @@ cudaError_t launch_analyze(const LaunchGeom& g, const Gf2Tables* d_tab, const vo
 cudaError_t launch_table_clear(const LaunchGeom& g, DedupTable t, cudaStream_t s);  // every key 0, every owner 0xFFFFFFFF
 cudaError_t launch_table_insert(const LaunchGeom& g, DedupTable t, const uint64_t* d_hash,
                                 const uint32_t* d_ref_or_null, uint64_t n, uint32_t origin,
-                                uint64_t index_base, cudaStream_t s);
+                                uint64_t index_base, cudaStream_t s, bool pending_only = false);
+// incremental K2 over a table that holds the parent alone: PARENT references at once, the rest left kRefPending
+cudaError_t launch_resolve_parent(const LaunchGeom& g, DedupTable t, uint64_t n_pages, const uint32_t* d_crc,
+                                  const uint64_t* d_hash, uint32_t* d_ref, ListView<uint32_t> parent_crc,
+                                  DevCounters* d_cnt, cudaStream_t s);
 cudaError_t launch_table_probe_lists(const LaunchGeom& g, DedupTable t, const ProbeLists& lists, cudaStream_t s);
 cudaError_t launch_resolve(const LaunchGeom& g, DedupTable t, uint64_t page0, uint64_t page1, const uint32_t* d_crc,
-                           const uint64_t* d_hash, uint32_t* d_ref, PeerCrcs crcs, DevCounters* d_cnt, cudaStream_t s);
+                           const uint64_t* d_hash, uint32_t* d_ref, PeerCrcs crcs, DevCounters* d_cnt, cudaStream_t s,
+                           bool pending_only = false);
 cudaError_t launch_verify_dups(const LaunchGeom& g, const void* d_image, uint64_t n_pages, uint32_t* d_ref, DevCounters* d_cnt,
                                cudaStream_t s);
 cudaError_t launch_compact(const LaunchGeom& g, const void* d_image, uint64_t n_pages, uint32_t* d_ref,

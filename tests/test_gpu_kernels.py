@@ -280,6 +280,29 @@ def test_dedup_rule_on_crafted_tables(ctx):
         0,                       # 7: zero page untouched
     ]
 
+    # a parent and no peers: the incremental K2 (the parent's table first, a second one for the pages it does not hold)
+    #        page:  0    1    2    3    4    5    6    7    8
+    h = arr([       33,  44,  44,  77,  77,  33,  88,  0,   77], i64)
+    crc = arr([     3,   4,   4,   6,   6,   3,   1,   7,   2], i32)
+    ref = arr([PENDING] * 7 + [0, PENDING], i64).to(i32)
+    parent = (arr([99, 33, 44, 33, 0], i64), arr([1, 3, 8, 3, 0], i32))  # hash 33 twice: the lower page owns it
+    ctx.dedup(crc, h, ref, parent=parent)
+    again = ref.clone()
+    ctx.dedup(crc, h, again, parent=parent)                              # deciding twice changes nothing
+    got = [int(x) & 0xFFFFFFFF for x in ref.cpu().tolist()]
+    assert got == [int(x) & 0xFFFFFFFF for x in again.cpu().tolist()]
+    assert got == [
+        3 << 29 | 1,             # 0: parent page 1 (not 3)
+        KEEP,                    # 1: parent holds hash 44 with another CRC: stored ...
+        KEEP,                    # 2: ... and its twin here does not refer to page 1 either: the parent owns the hash
+        KEEP,                    # 3: not in the parent; first page with hash 77
+        2 << 29 | 3,             # 4: duplicate of page 3
+        3 << 29 | 1,             # 5
+        KEEP,                    # 6
+        0,                       # 7: zero page untouched
+        KEEP,                    # 8: hash of page 3 with another CRC: stored
+    ]
+
 
 def test_dense_images_are_written_through_and_mixed_ones_are_not(ctx, oracle):
     """grit_pack_buffer samples a full image: where a long prefix would stay in place (no repeated page among the

@@ -12,7 +12,7 @@ CSRC = os.path.join(ROOT, "grit_b200", "csrc")
 
 @pytest.mark.skipif(shutil.which("nvcc") is None, reason="nvcc builds the host test (cuda_runtime.h in the headers)")
 def test_native_host_logic(tmp_path):
-    objs = [os.path.join(CSRC, o) for o in ("kernels.o", "api.o", "hostpipe.o", "host_util.o", "static_scratch.o")]
+    objs = [os.path.join(CSRC, o) for o in ("kernels.o", "api.o", "hostpipe.o", "host_util.o", "static_scratch.o", "comm.o")]
     if not all(os.path.exists(o) for o in objs):
         subprocess.run(["make", "-C", CSRC], check=True, capture_output=True)
     exe = tmp_path / "host_logic_test"

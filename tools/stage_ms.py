@@ -3,7 +3,7 @@ import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from grit_b200.buffers import Context
-PAGE, n = 4096, 3_921_026
+PAGE, n = 4096, int(os.environ.get("STAGE_PAGES", 3_921_026))
 ctx = Context(0)
 packed = torch.empty(n * PAGE, dtype=torch.uint8, device="cuda")
 base = None
