@@ -261,10 +261,10 @@ def test_dedup_rule_on_crafted_tables(ctx):
 
     def arr(vals, dt):
         return torch.tensor(vals, dtype=dt, device="cuda")
-    #        page:  0    1    2    3    4    5    6    7
-    h = arr([       11,  22,  11,  11,  33,  44,  55,  0], i64)
-    crc = arr([     1,   2,   1,   9,   3,   4,   5,   7], i32)     # page 3: hash of page 0, different CRC
-    ref = arr([PENDING] * 7 + [0], i64).to(i32)                    # page 7 is a zero page (never looked up)
+    #        page:  0    1    2    3    4    5    6    7    8
+    h = arr([       11,  22,  11,  11,  33,  44,  55,  0,   0], i64)
+    crc = arr([     1,   2,   1,   9,   3,   4,   5,   7,   5], i32)  # page 3: hash of page 0, different CRC
+    ref = arr([PENDING] * 7 + [0, PENDING], i64).to(i32)           # page 7 is a zero page (never looked up)
     parent = (arr([33, 44], i64), arr([3, 8], i32))                # hash 33 matches page 4 (CRC too); 44 collides (CRC differs)
     peers = [(arr([55, 22], i64), arr([5, 2], i32)), (arr([55], i64), arr([5], i32))]
     ctx.dedup(crc, h, ref, parent=parent, peers=peers)
@@ -278,13 +278,14 @@ def test_dedup_rule_on_crafted_tables(ctx):
         KEEP,                    # 5: parent holds hash 44 with another CRC: stored
         4 << 29 | 0 << 26 | 0,   # 6: both peers hold it; the lowest rank owns it
         0,                       # 7: zero page untouched
+        KEEP,                    # 8: hash 0 is the table's empty key (K1 never gives it): stored, never looked up
     ]
 
     # a parent and no peers: the incremental K2 (the parent's table first, a second one for the pages it does not hold)
     #        page:  0    1    2    3    4    5    6    7    8
-    h = arr([       33,  44,  44,  77,  77,  33,  88,  0,   77], i64)
-    crc = arr([     3,   4,   4,   6,   6,   3,   1,   7,   2], i32)
-    ref = arr([PENDING] * 7 + [0, PENDING], i64).to(i32)
+    h = arr([       33,  44,  44,  77,  77,  33,  88,  0,   77,  0], i64)
+    crc = arr([     3,   4,   4,   6,   6,   3,   1,   7,   2,   0], i32)
+    ref = arr([PENDING] * 7 + [0, PENDING, PENDING], i64).to(i32)
     parent = (arr([99, 33, 44, 33, 0], i64), arr([1, 3, 8, 3, 0], i32))  # hash 33 twice: the lower page owns it
     ctx.dedup(crc, h, ref, parent=parent)
     again = ref.clone()
@@ -301,6 +302,7 @@ def test_dedup_rule_on_crafted_tables(ctx):
         KEEP,                    # 6
         0,                       # 7: zero page untouched
         KEEP,                    # 8: hash of page 3 with another CRC: stored
+        KEEP,                    # 9: hash 0 (and the parent's padding entry has hash 0, CRC 0 too): stored
     ]
 
 
