@@ -42,7 +42,7 @@ bool is_pinned(const void* p) {
 
 // ------------------------------------------------------------------ PackStream
 PackStream::PackStream(grit_ctx* ctx, uint64_t total_pages, uint64_t chunk_pages)
-    : ctx_(ctx), total_pages_(total_pages), chunk_pages_(std::max<uint64_t>(chunk_pages, kCompactTile)) {}
+    : ctx_(ctx), total_pages_(total_pages), chunk_pages_(std::max<uint64_t>(chunk_pages, 256)) {}
 
 PackStream::~PackStream() {
   cudaSetDevice(ctx_->device);

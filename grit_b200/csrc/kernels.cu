@@ -658,11 +658,18 @@ __device__ __forceinline__ void st_status(unsigned long long* p, unsigned long l
   asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
-__global__ void __launch_bounds__(256)
-k_compact(const uint4* __restrict__ image, uint64_t n_pages, uint32_t* __restrict__ ref,
-          uint4* __restrict__ packed, uint64_t capacity_pages, uint64_t slot_base, int chained, int in_place,
-          unsigned long long* __restrict__ status, DevCounters* __restrict__ cnt) {
+// kPer pages per thread, 256 * kPer pages per tile.  One page per thread suits an image that stores most of its pages:
+// a tile is then hundreds of page copies, and short tiles keep the last blocks' tail short.  In an image of mostly
+// references (an incremental checkpoint) a 256-page tile is a dozen copies behind a fixed chain of L2 round trips
+// (ticket, ref words, look-back), and four pages per thread cut the number of such chains by four.
+template <int kPer>
+__device__ __forceinline__ void
+compact_body(const uint4* __restrict__ image, uint64_t n_pages, uint32_t* __restrict__ ref,
+             uint4* __restrict__ packed, uint64_t capacity_pages, uint64_t slot_base, int chained, int in_place,
+             unsigned long long* __restrict__ status, DevCounters* __restrict__ cnt) {
+  constexpr uint32_t kTile = 256u * kPer;
   __shared__ uint32_t s_tile, s_warp_cnt[8], s_excl;
+  __shared__ uint2 s_kind[8];
   in_place = in_place && cnt->dense_hint;  // the write-through K1 ran: pages in front of the first drop are in place
   // Nothing was dropped at all (no zero page met, no reference made): every page is stored, in its own slot, where the
   // write-through K1 already put it.  No scan, no look-back: one streaming pass over ref.
@@ -677,9 +684,9 @@ k_compact(const uint4* __restrict__ image, uint64_t n_pages, uint32_t* __restric
     }
     return;
   }
-  __shared__ uint16_t s_list[kCompactTile];
+  __shared__ uint16_t s_list[kTile];
   const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const uint32_t n_tiles = (uint32_t)((n_pages + kCompactTile - 1) / kCompactTile);
+  const uint32_t n_tiles = (uint32_t)((n_pages + kTile - 1) / kTile);
   // chained (streaming) mode: slots continue from the previous launch's total, which only
   // the device knows; the packed buffer then holds just this launch's pages, from index 0.
   const uint64_t ref_base = chained ? cnt->slot_base : slot_base;
@@ -702,18 +709,31 @@ k_compact(const uint4* __restrict__ image, uint64_t n_pages, uint32_t* __restric
       }
       return;
     }
-    const uint64_t p = (uint64_t)tile * kCompactTile + threadIdx.x;
-    const uint32_t r = p < n_pages ? ref[p] : 0u;
-    const bool keep = r == kRefKeep;
-
-    const uint32_t bal = __ballot_sync(0xFFFFFFFFu, keep);
-    if (lane == 0) s_warp_cnt[warp] = __popc(bal);
-    // per-kind page counts for the stats (a few smem-free block reductions)
-    const uint32_t kind = keep ? 1u : (p < n_pages ? r >> 29 : 7u);
-    const int n_zero = __syncthreads_count(kind == 0u);
-    const int n_dup = __syncthreads_count(kind == 2u);
-    const int n_par = __syncthreads_count(kind == 3u);
-    const int n_peer = __syncthreads_count(kind == 4u);
+    // kPer consecutive pages per thread
+    const uint64_t p0 = (uint64_t)tile * kTile + (uint32_t)kPer * threadIdx.x;
+    uint32_t keepm = 0, pack_a = 0, pack_b = 0;  // bit j: page p0 + j is stored; zero | dup << 16; parent | peer << 16
+#pragma unroll
+    for (int j = 0; j < kPer; j++) {
+      const bool in = p0 + j < n_pages;
+      const uint32_t r = in ? ref[p0 + j] : 0u;
+      const bool keep = r == kRefKeep;
+      keepm |= keep ? 1u << j : 0u;
+      const uint32_t kind = keep ? 1u : (in ? r >> 29 : 7u);
+      pack_a += (kind == 0u ? 1u : 0u) + (kind == 2u ? 1u << 16 : 0u);
+      pack_b += (kind == 3u ? 1u : 0u) + (kind == 4u ? 1u << 16 : 0u);
+    }
+    const uint32_t mine = __popc(keepm);
+    uint32_t inc = mine;  // stored pages of this warp up to and including this thread
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+      inc += lane >= (uint32_t)o ? t : 0u;
+    }
+    pack_a = __reduce_add_sync(0xFFFFFFFFu, pack_a);
+    pack_b = __reduce_add_sync(0xFFFFFFFFu, pack_b);
+    if (lane == 31) s_warp_cnt[warp] = inc;
+    if (lane == 0) s_kind[warp] = make_uint2(pack_a, pack_b);
+    __syncthreads();
 
     uint32_t before = 0, total = 0;
 #pragma unroll
@@ -722,11 +742,19 @@ k_compact(const uint4* __restrict__ image, uint64_t n_pages, uint32_t* __restric
       before += w < (int)warp ? c : 0u;
       total += c;
     }
-    sum_zero += n_zero;
-    sum_keep += total;
-    sum_dup += n_dup;
-    sum_par += n_par;
-    sum_peer += n_peer;
+    if (threadIdx.x == 0) {
+      uint32_t ka = 0, kb = 0;  // a block's sums stay below 2^16 per field
+#pragma unroll
+      for (int w = 0; w < 8; w++) {
+        ka += s_kind[w].x;
+        kb += s_kind[w].y;
+      }
+      sum_zero += ka & 0xFFFFu;
+      sum_dup += ka >> 16;
+      sum_par += kb & 0xFFFFu;
+      sum_peer += kb >> 16;
+      sum_keep += total;
+    }
 
     if (warp == 0) {
       if (lane == 0) st_status(&status[tile], (tile == 0 ? kFlagIncl : kFlagAgg) | total);
@@ -758,25 +786,36 @@ k_compact(const uint4* __restrict__ image, uint64_t n_pages, uint32_t* __restric
         }
       }
     }
-    const uint32_t rank = before + __popc(bal & ((1u << lane) - 1));
-    if (keep) s_list[rank] = (uint16_t)threadIdx.x;
+    const uint32_t rank0 = before + inc - mine;
+    {
+      uint32_t k = rank0;
+#pragma unroll
+      for (int j = 0; j < kPer; j++)
+        if (keepm >> j & 1u) s_list[k++] = (uint16_t)((uint32_t)kPer * threadIdx.x + j);
+    }
     __syncthreads();
     const uint64_t first_slot = out_base + s_excl;
-    if (keep) {
-      ref[p] = 1u << 29 | (uint32_t)(ref_base + s_excl + rank);
-      if (first_slot + rank >= capacity_pages) atomicAdd(&cnt->overflow, 1ull);
+    {
+      uint32_t k = rank0;
+#pragma unroll
+      for (int j = 0; j < kPer; j++)
+        if (keepm >> j & 1u) {
+          ref[p0 + j] = 1u << 29 | (uint32_t)(ref_base + s_excl + k);
+          if (first_slot + k >= capacity_pages) atomicAdd(&cnt->overflow, 1ull);
+          k++;
+        }
     }
     // after a write-through K1 a tile whose pages all keep their own index is already in place
-    const uint64_t tile_base = (uint64_t)tile * kCompactTile;
-    const uint32_t tile_pages = (uint32_t)(n_pages - tile_base < kCompactTile ? n_pages - tile_base : kCompactTile);
+    const uint64_t tile_base = (uint64_t)tile * kTile;
+    const uint32_t tile_pages = (uint32_t)(n_pages - tile_base < kTile ? n_pages - tile_base : kTile);
     const bool tile_in_place = in_place && first_slot == tile_base && total == tile_pages && tile_base >= cnt->through_from;
     // copy: one page per warp per step, two steps in flight
     for (uint32_t k = tile_in_place ? total : warp; k < total; k += 16) {
       const uint32_t k2 = k + 8;
       const bool two = k2 < total;
       const uint64_t sa = first_slot + k, sb = first_slot + k2;
-      const uint4* a = image + ((uint64_t)tile * kCompactTile + s_list[k]) * 256 + lane;
-      const uint4* b = image + ((uint64_t)tile * kCompactTile + s_list[two ? k2 : k]) * 256 + lane;
+      const uint4* a = image + ((uint64_t)tile * kTile + s_list[k]) * 256 + lane;
+      const uint4* b = image + ((uint64_t)tile * kTile + s_list[two ? k2 : k]) * 256 + lane;
       uint4 va[8], vb[8];
 #pragma unroll
       for (int j = 0; j < 8; j++) va[j] = ldg_stream(a + 32 * j);
@@ -795,6 +834,28 @@ k_compact(const uint4* __restrict__ image, uint64_t n_pages, uint32_t* __restric
     }
     __syncthreads();  // s_tile, s_list reused by the next tile
   }
+}
+
+// K2 counted the references it made.  More than half of the pages: the wide tiles take the image (k_compact_wide),
+// else the short ones; the device knows, so both kernels are launched and one of them returns at once.
+__device__ __forceinline__ bool compact_is_sparse(const DevCounters* cnt, uint64_t n_pages) {
+  return (uint64_t)cnt->n_nonkeep * 2 > n_pages;
+}
+
+__global__ void __launch_bounds__(256)
+k_compact(const uint4* __restrict__ image, uint64_t n_pages, uint32_t* __restrict__ ref,
+          uint4* __restrict__ packed, uint64_t capacity_pages, uint64_t slot_base, int chained, int in_place,
+          unsigned long long* __restrict__ status, DevCounters* __restrict__ cnt, int paired) {
+  if (paired && compact_is_sparse(cnt, n_pages)) return;
+  compact_body<1>(image, n_pages, ref, packed, capacity_pages, slot_base, chained, in_place, status, cnt);
+}
+
+__global__ void __launch_bounds__(256)
+k_compact_wide(const uint4* __restrict__ image, uint64_t n_pages, uint32_t* __restrict__ ref,
+               uint4* __restrict__ packed, uint64_t capacity_pages, uint64_t slot_base, int in_place,
+               unsigned long long* __restrict__ status, DevCounters* __restrict__ cnt) {
+  if (!compact_is_sparse(cnt, n_pages)) return;
+  compact_body<4>(image, n_pages, ref, packed, capacity_pages, slot_base, 0, in_place, status, cnt);
 }
 
 // ------------------------------------------------------------------ K1+K2+K3 in one pass, pages parked in TMEM
@@ -1470,9 +1531,14 @@ cudaError_t launch_compact(const LaunchGeom& g, const void* d_image, uint64_t n_
                            void* d_packed, uint64_t capacity_pages, uint64_t slot_base, bool chained,
                            unsigned long long* d_tile_status, DevCounters* d_cnt, cudaStream_t s, bool in_place) {
   if (!n_pages) return cudaSuccess;
+  const int place = (in_place && !chained && slot_base == 0) ? 1 : 0;
   k_compact<<<grid_for(g, n_pages, kCompactTile, 8), 256, 0, s>>>(
       static_cast<const uint4*>(d_image), n_pages, d_ref, static_cast<uint4*>(d_packed), capacity_pages,
-      slot_base, chained ? 1 : 0, (in_place && !chained && slot_base == 0) ? 1 : 0, d_tile_status, d_cnt);
+      slot_base, chained ? 1 : 0, place, d_tile_status, d_cnt, chained ? 0 : 1);
+  if (!chained)  // a chained launch's slot base is the device's; its chunks are short, the plain tiles do
+    k_compact_wide<<<grid_for(g, n_pages, 4 * kCompactTile, 8), 256, 0, s>>>(
+        static_cast<const uint4*>(d_image), n_pages, d_ref, static_cast<uint4*>(d_packed), capacity_pages,
+        slot_base, place, d_tile_status, d_cnt);
   return cudaGetLastError();
 }
 

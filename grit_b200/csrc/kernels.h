@@ -13,7 +13,7 @@ constexpr uint32_t kPage = 4096;
 constexpr uint32_t kRefPending = 0xFFFFFFFFu;  // K1: non-zero page, not yet resolved
 constexpr uint32_t kRefKeep = 0xFFFFFFFEu;     // K2: must be stored, slot not yet assigned
 constexpr uint32_t kOriginSelf = 15;
-constexpr uint32_t kCompactTile = 256;  // pages per compaction tile
+constexpr uint32_t kCompactTile = 256;  // pages per compaction tile (k_compact_wide: four times that)
 
 // table[hash64] = lowest (origin << 26 | page index); origin 0 parent, 1+r peer r, 15 self
 // key and owner share a 16-byte slot: one DRAM sector per insert, probe or look-up instead of two
