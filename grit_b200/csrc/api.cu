@@ -104,6 +104,9 @@ int dedup_views_async(grit_ctx* ctx, uint64_t n_pages, const uint32_t* d_crc, co
                       const PeerCrcs& crcs, const ProbeLists& lists, cudaStream_t s, char* err, size_t errlen,
                       cudaEvent_t lists_ready) {
   DedupTable t{};
+  // K2 counts the references it makes (K3 picks its tiles by it): from zero for every image, also for callers of the
+  // stage entry points, whose K1 does not reset it
+  GRIT_CUDA(cudaMemsetAsync(&ctx->d_cnt->n_nonkeep, 0, sizeof(unsigned int), s));
   bool peers_on = false;
   for (int o = 1; o < 9; o++) peers_on = peers_on || (lists.n[o] && lists.hash[o]);
   if (!peers_on && lists.n[0] && lists.hash[0] && lists.hash[0].stride == 0 && crcs.parent) {
